@@ -1,0 +1,30 @@
+"""Side-stream helper (reference: utils/helpers.py:6-28).
+
+Same protocol: STORE_STREAM waits for the default stream, the function runs
+inside `with STORE_STREAM`, inputs are recorded on STORE_STREAM and tensor
+outputs on the default stream.  The native wrappers always launch on
+torch.cuda.current_stream(), so they follow the `with` block.
+"""
+from collections.abc import Callable
+
+import torch
+
+
+def maybe_execute_in_stream(fn: Callable, *args, STORE_STREAM: torch.cuda.Stream = None, **kwargs):
+    if STORE_STREAM is None:
+        return fn(*args, **kwargs)
+    tensors = [a for a in args if isinstance(a, torch.Tensor)]
+    tensors += [v for v in kwargs.values() if isinstance(v, torch.Tensor)]
+    obj = getattr(fn, "__self__", None)
+    if isinstance(obj, torch.Tensor):
+        tensors.append(obj)
+    STORE_STREAM.wait_stream(torch.cuda.default_stream())
+    with torch.cuda.stream(STORE_STREAM):
+        output = fn(*args, **kwargs)
+    for t in tensors:
+        t.record_stream(STORE_STREAM)
+    outs = output if isinstance(output, tuple) else (output,)
+    for o in outs:
+        if isinstance(o, torch.Tensor):
+            o.record_stream(torch.cuda.default_stream())
+    return output

@@ -1,0 +1,123 @@
+// Shared host/device helpers for libcompactor_sm100.so (sm_100a only).
+#pragma once
+
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/cvllm.h"
+
+namespace cvllm {
+
+// ---------------------------------------------------------------------------
+// host-side error plumbing
+// ---------------------------------------------------------------------------
+void set_last_error(const char* msg);
+
+#define CVLLM_CHECK_ARG(cond)                                                  \
+  do {                                                                         \
+    if (!(cond)) {                                                             \
+      ::cvllm::set_last_error("argument check failed: " #cond);                \
+      return CVLLM_E_ARG;                                                      \
+    }                                                                          \
+  } while (0)
+
+#define CVLLM_CHECK_SUPPORTED(cond)                                            \
+  do {                                                                         \
+    if (!(cond)) {                                                             \
+      ::cvllm::set_last_error("unsupported configuration: " #cond);            \
+      return CVLLM_E_UNSUPPORTED;                                              \
+    }                                                                          \
+  } while (0)
+
+#define CVLLM_CHECK_ALIGN(cond)                                                \
+  do {                                                                         \
+    if (!(cond)) {                                                             \
+      ::cvllm::set_last_error("alignment check failed: " #cond);               \
+      return CVLLM_E_ALIGN;                                                    \
+    }                                                                          \
+  } while (0)
+
+#define CVLLM_CHECK_CUDA(expr)                                                 \
+  do {                                                                         \
+    cudaError_t _e = (expr);                                                   \
+    if (_e != cudaSuccess) {                                                   \
+      ::cvllm::set_last_error(cudaGetErrorString(_e));                         \
+      return CVLLM_E_CUDA;                                                     \
+    }                                                                          \
+  } while (0)
+
+#define CVLLM_CHECK_LAUNCH() CVLLM_CHECK_CUDA(cudaPeekAtLastError())
+
+inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+int sm_count();
+
+// ---------------------------------------------------------------------------
+// small device helpers
+// ---------------------------------------------------------------------------
+__host__ __device__ __forceinline__ int cdiv(int a, int b) { return (a + b - 1) / b; }
+
+__device__ __forceinline__ uint4 ldg_nc_v4(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+
+__device__ __forceinline__ void stg_na_v4(void* p, const uint4& v) {
+  asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x),
+               "r"(v.y), "r"(v.z), "r"(v.w)
+               : "memory");
+}
+
+__device__ __forceinline__ float ex2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// float pair -> packed 16-bit pair (lo = a, hi = b)
+template <bool BF16>
+__device__ __forceinline__ uint32_t pack2(float a, float b) {
+  uint32_t r;
+  if constexpr (BF16) {
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
+  } else {
+    asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
+  }
+  return r;
+}
+
+template <bool BF16>
+__device__ __forceinline__ float2 unpack2(uint32_t v) {
+  if constexpr (BF16) {
+    return make_float2(__uint_as_float(v << 16), __uint_as_float(v & 0xffff0000u));
+  } else {
+    __half2 h = *reinterpret_cast<__half2*>(&v);
+    return __half22float2(h);
+  }
+}
+
+// order-preserving fp32 -> uint32 key; NaN ranks above +inf (torch.topk order)
+__host__ __device__ __forceinline__ uint32_t score_key(uint32_t bits) {
+  if ((bits & 0x7fffffffu) > 0x7f800000u) return 0xffffffffu;  // NaN
+  return (bits & 0x80000000u) ? ~bits : (bits | 0x80000000u);
+}
+
+}  // namespace cvllm

@@ -1,0 +1,220 @@
+/*
+ * cvllm.h — C ABI of libcompactor_sm100.so
+ *
+ * Drop-in boundary for the attention + KV-compression hot path of
+ * vnchari/compactor-vllm, rebuilt as hand-written sm_100a CUDA.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless the name ends in `_host`
+ *   - every launch function takes the CUDA stream (a cudaStream_t passed as
+ *     void*) last, launches on it and returns without synchronising
+ *   - return value: 0 = launched; negative = argument error detected on the
+ *     host before any launch (see CVLLM_E_*); nothing is thrown
+ *   - no torch types, no global state (TMA descriptors are rebuilt per call)
+ *   - all index tensors are int32 unless stated; scores are fp32
+ *   - strides are in ELEMENTS of the tensor's dtype
+ *   - `dtype`: CVLLM_F16 or CVLLM_BF16 (the arithmetic is always fp32
+ *     accumulate)
+ *
+ * Each entry point cites the reference interface it replaces
+ * (paths relative to the reference's src/compactor_vllm/).
+ */
+#ifndef CVLLM_H_
+#define CVLLM_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CVLLM_ABI_VERSION 1
+
+enum { CVLLM_F16 = 0, CVLLM_BF16 = 1 };
+
+enum {
+  CVLLM_OK = 0,
+  CVLLM_E_ARG = -1,         /* bad shape / size / null pointer            */
+  CVLLM_E_UNSUPPORTED = -2, /* head_dim / group size / page size combo    */
+  CVLLM_E_WORKSPACE = -3,   /* workspace too small                        */
+  CVLLM_E_CUDA = -4,        /* launch or driver-entry-point failure       */
+  CVLLM_E_ALIGN = -5        /* pointer / stride not 16-byte aligned       */
+};
+
+typedef void* cvllm_stream_t;
+
+/* ABI version + last CUDA error string (host, static storage). */
+int cvllm_abi_version(void);
+const char* cvllm_last_error(void);
+
+/* ------------------------------------------------------------------------
+ * Store path
+ * --------------------------------------------------------------------- */
+
+/* decode_store_kv — kv_cache/store_kv_cache.py:374-466 (kernel :374-416).
+ * Append key[b,h,:], value[b,h,:] at logical position bh_lens[b,h] of head
+ * (batch_mapping[b], h); bh_lens[b,h] += 1.  Rows with
+ * batch_mapping[b] == reserved_batch are skipped. */
+int cvllm_decode_store_kv(const void* key, const void* value,
+                          int64_t sk_b, int64_t sk_h, int64_t sv_b, int64_t sv_h,
+                          const int32_t* batch_mapping, int32_t* bh_lens,
+                          const int32_t* page_table, void* k_cache, void* v_cache,
+                          int B, int HKV, int D, int PS, int NLP, int elem_bytes,
+                          int reserved_batch, cvllm_stream_t stream);
+
+/* prefill_store_all_kv — kv_cache/store_kv_cache.py:251-371.
+ * Scatter every (token, head) row of the packed batch to logical position
+ * bh_lens[b,h] + t, then bh_lens[b,:] += len_b (the reference's
+ * `bh_lens += cu_seqlens_k.diff()[:,None]`, :371). */
+int cvllm_prefill_store_all(const void* keys, const void* vals,
+                            int64_t sk_n, int64_t sk_h, int64_t sv_n, int64_t sv_h,
+                            const int32_t* cu_seqlens_k, const int32_t* batch_mapping,
+                            int32_t* bh_lens, const int32_t* page_table,
+                            void* k_cache, void* v_cache,
+                            int B, int N, int HKV, int D, int PS, int NLP,
+                            int elem_bytes, cvllm_stream_t stream);
+
+/* scatter_to_page_table — kv_cache/write_page_table.py:6-95.
+ * page_table[l,h,curr[l,h]+i] = new_phys[cum[l,h]+i] for i < add[l,h];
+ * the exclusive prefix sum `cum` is computed inside (replaces torch.cumsum,
+ * :42-44).  pt_stride_* in int32 elements. */
+int cvllm_scatter_pages(const int32_t* add_pages, const int32_t* new_phys,
+                        const int32_t* curr_pages, int32_t* page_table,
+                        int64_t pt_stride_l, int64_t pt_stride_h, int64_t pt_stride_p,
+                        int L, int H, int max_pages_per_head, cvllm_stream_t stream);
+
+/* ------------------------------------------------------------------------
+ * Selection + compaction
+ * --------------------------------------------------------------------- */
+
+/* scores_to_retain_indices — compression/common.py:171-243.
+ * Per sequence b: full descending ranking of its len_b*H scores, ties broken
+ * by ascending flat index, NaN ranked above +inf (torch.topk order).  Output
+ * int64 [B, k_eff], k_eff = min(top_k, max_k_len*H); entry = global flat
+ * index (cu[b]+tok)*H + head.  Positions >= len_b*H hold the padded-slot
+ * indices the reference would produce (cu[b]*H + padded position). */
+size_t cvllm_rank_scores_workspace_bytes(int B, int H, int max_k_len);
+int cvllm_rank_scores(const float* scores, int64_t s_stride_n,
+                      const int32_t* cu_seqlens_k, int B, int H, int max_k_len,
+                      int top_k, int64_t* out_indices, void* workspace,
+                      size_t workspace_bytes, cvllm_stream_t stream);
+
+/* prefill_store_topk_kv — kv_cache/store_kv_cache.py:9-248 (K4 + K5), index
+ * flavour: `indices` is the [B, max_sel] ranking (int32 or int64 by
+ * idx_bytes).  The first num_retain[b] entries are stored, then (if
+ * pad_to_page) each head is topped up to a page multiple with the next
+ * entries of that head (:205-248).  Rows are written in ascending token order
+ * per head (the reference's order is atomic-nondeterministic). */
+size_t cvllm_store_topk_workspace_bytes(int B, int H, int N, int max_sel);
+int cvllm_prefill_store_topk_idx(const void* keys, const void* vals,
+                                 int64_t sk_n, int64_t sk_h, int64_t sv_n, int64_t sv_h,
+                                 const void* indices, int idx_bytes, int max_sel,
+                                 const int32_t* num_retain, const int32_t* cu_seqlens_k,
+                                 const int32_t* batch_mapping, int32_t* bh_lens,
+                                 const int32_t* page_table, void* k_cache, void* v_cache,
+                                 int B, int N, int HKV, int D, int PS, int NLP,
+                                 int elem_bytes, int pad_to_page, int reserved_batch,
+                                 void* workspace, size_t workspace_bytes,
+                                 cvllm_stream_t stream);
+
+/* extract_and_store_top_kv — compression/common.py:126-168, fused: scores ->
+ * radix-select (global top num_retain[b], then per-head top n_h) -> gather
+ * into the paged cache.  Same kept sets as rank + store_topk_idx with the full
+ * ranking (top_k >= max_len*H, the engine's setting, utils/arguments.py
+ * :208-211). */
+size_t cvllm_select_store_workspace_bytes(int B, int H, int N);
+int cvllm_select_store_topk(const float* scores, int64_t s_stride_n,
+                            const void* keys, const void* vals,
+                            int64_t sk_n, int64_t sk_h, int64_t sv_n, int64_t sv_h,
+                            const int32_t* num_retain, const int32_t* cu_seqlens_k,
+                            const int32_t* batch_mapping, int32_t* bh_lens,
+                            const int32_t* page_table, void* k_cache, void* v_cache,
+                            int B, int N, int HKV, int D, int PS, int NLP,
+                            int elem_bytes, int pad_to_page, int reserved_batch,
+                            void* workspace, size_t workspace_bytes,
+                            cvllm_stream_t stream);
+
+/* ------------------------------------------------------------------------
+ * Attention
+ * --------------------------------------------------------------------- */
+
+/* head_sparse_decode_attention — attention/sparse_decode_kernel.py:10-165
+ * (K2 :247-388 + K3 :392-435).  One query token per sequence against the
+ * per-(b,h) paged rows; balanced split over 128-token units with an in-kernel
+ * LSE merge.  Rows with L==0 are written as zeros.  `num_ctas` <= 0 picks
+ * 2 * SM count.  Graph-capturable: no host sync, fixed grid. */
+size_t cvllm_decode_attention_workspace_bytes(int B, int HQ, int HKV, int D, int num_ctas);
+int cvllm_decode_attention(const void* q, void* out, const void* k_cache, const void* v_cache,
+                           const int32_t* seq_lens_bh, const int32_t* page_table,
+                           const int32_t* batch_mapping, void* workspace,
+                           size_t workspace_bytes, int B, int HQ, int HKV, int D,
+                           int PS, int NLP, float sm_scale, int dtype, int num_ctas,
+                           cvllm_stream_t stream);
+
+/* causal_sparse_varlen_with_cache — attention/sparse_varlen_kernel.py:11-197
+ * (K1 :265-519).  Causal attention of the packed new tokens over
+ * [cached prefix of (b,h) || new K/V of b]; tcgen05/TMEM/TMA kernel. */
+int cvllm_prefill_attention(const void* q, const void* k, const void* v, void* out,
+                            const void* k_cache, const void* v_cache,
+                            const int32_t* seq_lens_bh, const int32_t* page_table,
+                            const int32_t* batch_mapping, const int32_t* cu_seqlens_q,
+                            int B, int N, int HQ, int HKV, int D, int PS, int NLP,
+                            int64_t cache_rows, int64_t q_stride_n, int64_t k_stride_n,
+                            int64_t v_stride_n, int64_t o_stride_n, int max_seqlen_q,
+                            float sm_scale, int dtype, cvllm_stream_t stream);
+
+/* ------------------------------------------------------------------------
+ * Scoring
+ * --------------------------------------------------------------------- */
+
+/* approximate_leverage_scores — compression/compactor.py:113-221 (+ z-score
+ * :224-269).  chunk_offsets[n_chunks+1] are packed-token offsets of the
+ * (<= chunk_size) chunks produced by split_into_chunks (:62-110).  out is
+ * [N, HKV] in `dtype` (the reference returns K's dtype). */
+size_t cvllm_leverage_scores_workspace_bytes(int N, int HKV, int sketch, int n_chunks);
+int cvllm_leverage_scores(const void* k_pre, int64_t k_stride_n, int64_t k_stride_h,
+                          const int32_t* chunk_offsets, int n_chunks, int max_chunk,
+                          const void* phi, void* out_scores, int N, int HKV, int D,
+                          int sketch, float regularizer, int normalize, int dtype,
+                          void* workspace, size_t workspace_bytes, cvllm_stream_t stream);
+
+/* non_causal_attn_scores — compression/compactor.py:338-599.  Chunk-local
+ * softmax column sums, per-sequence z-score, + blend*accum, protected
+ * first/last tokens <- +inf.  out fp32 [N, HKV]. accum may be NULL;
+ * accum_dtype: 2 = fp32, else CVLLM_F16/BF16.  prot_first/prot_last may be
+ * NULL (device int32 [B]). */
+size_t cvllm_chunk_attn_scores_workspace_bytes(int B, int N, int HKV, int chunk);
+int cvllm_chunk_attn_scores(const void* q, const void* k, int64_t q_stride_n,
+                            int64_t k_stride_n, const int32_t* cu_seqlens,
+                            int B, int N, int HQ, int HKV, int D, int chunk,
+                            int max_seqlen, float sm_scale, int normalize,
+                            const void* accum, int accum_dtype, int64_t accum_stride_n,
+                            float blend, const int32_t* prot_first,
+                            const int32_t* prot_last, float* out, int dtype,
+                            void* workspace, size_t workspace_bytes,
+                            cvllm_stream_t stream);
+
+/* query_aware_key_scores — compression/snapkv.py:39-276,332-448.  SnapKV:
+ * last-w queries x G heads against keys [0, L-w), softmax over those keys,
+ * column sums, causal `kpool`-tap mean pool inside `pool_segment`-key
+ * segments (the reference's autotuned BLOCK_K, :160-168,253-262), window
+ * keys <- +inf.  No logits scratch. */
+size_t cvllm_snapkv_scores_workspace_bytes(int B, int N, int HQ, int HKV, int w);
+int cvllm_snapkv_scores(const void* q, const void* k, int64_t q_stride_n,
+                        int64_t k_stride_n, const int32_t* cu_seqlens_q,
+                        const int32_t* cu_seqlens_k, int w, int B, int Nk, int HQ,
+                        int HKV, int D, int max_seqlen_k, float sm_scale, int kpool,
+                        int pool_segment, float* out, int dtype, void* workspace,
+                        size_t workspace_bytes, cvllm_stream_t stream);
+
+/* ------------------------------------------------------------------------
+ * Self tests (device sanity for descriptor encodings; used by tests only)
+ * --------------------------------------------------------------------- */
+int cvllm_selftest_umma(const void* a, const void* b, float* d, int mode,
+                        uint32_t lbo, uint32_t sbo, int dtype, cvllm_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CVLLM_H_ */
