@@ -436,14 +436,20 @@ extern "C" int cvllm_decode_attention(const void* q, void* out, const void* k_ca
   p.scale_log2 = sm_scale * 1.4426950408889634f;
 
   const size_t smem = (((BH + 1) * 4 + 15) & ~(size_t)15) + (size_t)(kDecWarps + 1) * 8 * (D + 2) * 4;
-  CVLLM_CHECK_SUPPORTED(smem <= 200 * 1024);
-  if (dtype == CVLLM_BF16) {
+  constexpr int kMaxSmem = 200 * 1024;
+  CVLLM_CHECK_SUPPORTED(smem <= (size_t)kMaxSmem);
+  // raise the dynamic-smem cap once per process (not a stream op; kept out of graph capture)
+  static bool attr_set = false;
+  if (!attr_set) {
     CVLLM_CHECK_CUDA(cudaFuncSetAttribute(decode_attn_kernel<true, 128>,
-                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxSmem));
+    CVLLM_CHECK_CUDA(cudaFuncSetAttribute(decode_attn_kernel<false, 128>,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxSmem));
+    attr_set = true;
+  }
+  if (dtype == CVLLM_BF16) {
     decode_attn_kernel<true, 128><<<C, kDecThreads, smem, st>>>(p);
   } else {
-    CVLLM_CHECK_CUDA(cudaFuncSetAttribute(decode_attn_kernel<false, 128>,
-                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     decode_attn_kernel<false, 128><<<C, kDecThreads, smem, st>>>(p);
   }
   CVLLM_CHECK_LAUNCH();
