@@ -18,6 +18,7 @@
 //     a scratch slot; the CTA that completes a head merges (atomic ticket)
 // HBM-bound: 4*D bytes per cached (token, head) — see DESIGN.md.
 #include "common.cuh"
+#include "mma.cuh"
 
 namespace cvllm {
 
@@ -38,34 +39,6 @@ struct DecodeParams {
   int B, HQ, HKV, G, PS, NLP;
   float scale_log2;
 };
-
-template <bool BF16>
-__device__ __forceinline__ void mma16816(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2,
-                                         uint32_t a3, uint32_t b0, uint32_t b1) {
-  if constexpr (BF16) {
-    asm volatile(
-        "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, "
-        "{%0,%1,%2,%3};"
-        : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
-        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
-  } else {
-    asm volatile(
-        "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, "
-        "{%0,%1,%2,%3};"
-        : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
-        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
-  }
-}
-
-__device__ __forceinline__ uint32_t movmatrix_trans(uint32_t a) {
-  uint32_t d;
-  asm volatile("movmatrix.sync.aligned.m8n8.trans.b16 %0, %1;" : "=r"(d) : "r"(a));
-  return d;
-}
-
-__device__ __forceinline__ uint32_t u4_get(const uint4& v, int i) {
-  return i == 0 ? v.x : (i == 1 ? v.y : (i == 2 ? v.z : v.w));
-}
 
 // One warp's 16-key slice: K rows r / r+8 (4 chunks each), V for 4 keys x 2 chunks.
 struct Slice {

@@ -220,7 +220,7 @@ def gen_stores():
     scores = torch.randn((N, H), generator=gen)
     scores[:2] = float("inf")
     scores[cu[1]:cu[1] + 1] = float("inf")
-    retain = torch.tensor([40, 3, 100], dtype=torch.int32)
+    retain = torch.tensor([40, 6, 100], dtype=torch.int32)  # > the 4 tied +inf entries of seq 1: no tie at the cut
     idx = scores_to_retain_indices(scores, cu, max(lens), max(lens) * H, H)
     kc, vc, bl = k_cache0.clone(), v_cache0.clone(), prefix.clone()
     skc.prefill_store_topk_kv(new_keys=keys, new_vals=vals, indices_topk=idx,
