@@ -19,6 +19,8 @@
 //
 // TMEM: S0 [0,128) S1 [128,256) O [256,384)  (fp32 columns, 128 lanes).
 // Tensor-pipe bound: 4*D flops per (query row, key) pair — see DESIGN.md.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "tma.cuh"
 
@@ -42,6 +44,7 @@ struct PrefillParams {
   int B, HQ, HKV, G, PS, NLP;
   int64_t o_stride_n;
   float scale_log2;
+  float rescale_threshold;
 };
 
 struct PrefillSmem {
@@ -53,7 +56,8 @@ struct PrefillSmem {
   uint64_t k_full[kStages], k_empty[kStages];
   uint64_t v_full[kStages], v_empty[kStages];
   uint64_t s_full[2], p_full[2];
-  uint64_t o_done;
+  uint64_t o_done;   // one phase per PV(i): conditional O-correction waits (at most one phase behind)
+  uint64_t o_final;  // single phase: last PV complete (the epilogue may be >1 phase behind o_done)
   uint32_t tmem_base;
 };
 
@@ -92,6 +96,7 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_const
       mbar_init(&sm.p_full[s], 128);
     }
     mbar_init(&sm.o_done, 1);
+    mbar_init(&sm.o_final, 1);
     mbar_fence_init();
   }
   if (warp == 1) {
@@ -184,6 +189,7 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_const
         }
         umma_commit(&sm.v_empty[st]);
         umma_commit(&sm.o_done);
+        if (i == n_tiles - 1) umma_commit(&sm.o_final);
       }
       __syncwarp();
     };
@@ -250,7 +256,7 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_const
 #pragma unroll
       for (int c = 1; c < kBN; ++c) mx = fmaxf(mx, s[c]);
       const float m_new = fmaxf(m_ref, mx * p.scale_log2);
-      const bool need = (j == 0) || (m_new > m_ref + kRescaleThreshold);
+      const bool need = (j == 0) || (m_new > m_ref + p.rescale_threshold);
       if (__any_sync(0xffffffffu, need)) {
         const float alpha = ex2(m_ref - m_new);  // m_ref == -inf on the first tile -> 0
         m_ref = m_new;
@@ -293,7 +299,9 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_const
     }
 
     // ---- epilogue: O / l -> out ----
-    mbar_wait(&sm.o_done, (n_tiles - 1) & 1);
+    // NOT o_done: only PV(n-3) is known complete here, and a parity wait two phases ahead
+    // of the barrier passes spuriously.
+    mbar_wait(&sm.o_final, 0);
     tc_fence_after();
     const float inv = l > 0.f ? 1.f / l : 0.f;
     char* orow = reinterpret_cast<char*>(p.out) +
@@ -473,6 +481,9 @@ extern "C" int cvllm_prefill_attention(const void* q, const void* k, const void*
   p.B = B; p.HQ = HQ; p.HKV = HKV; p.G = HQ / HKV; p.PS = PS; p.NLP = NLP;
   p.o_stride_n = o_stride_n;
   p.scale_log2 = sm_scale * 1.4426950408889634f;
+  p.rescale_threshold = kRescaleThreshold;
+  // test hook: 0 forces an O rescale whenever a row max grows (exercises the correction path)
+  if (const char* e = getenv("CVLLM_PREFILL_THRESHOLD")) p.rescale_threshold = (float)atof(e);
 
   const size_t smem = sizeof(PrefillSmem) + 1024;
   const dim3 grid((max_seqlen_q + kBM - 1) / kBM, HQ, B);

@@ -101,3 +101,21 @@ def test_prefill_bf16_16k_single_sequence():
     ref = torch_prefill_fp32(q, k, v, kc, vc, lens, pt, bm, cu, HKV, PS)
     assert (out.float() - ref).abs().max().item() <= ATOL[dtype]
     assert rel_err(out, ref) <= REL[dtype]
+
+
+@pytest.mark.parametrize("threshold", ["0", "8"])
+def test_prefill_correction_path(threshold, monkeypatch):
+    """A 1-key first tile makes later tiles raise the running max by far more than the lazy-rescale
+    threshold, so the O-correction path runs; threshold 0 (test hook) forces it on every increase."""
+    monkeypatch.setenv("CVLLM_PREFILL_THRESHOLD", threshold)
+    dtype, HQ, HKV, D, PS = torch.bfloat16, 8, 2, 128, 128
+    lens = [[1, 129], [257, 1]]
+    kc, vc, pt, bm = make_paged(2, HKV, D, PS, lens, dtype, DEV, seed=13, poison=True)
+    cu = torch.tensor([0, 700, 764], dtype=torch.int32, device=DEV)
+    q, k, v = fused_qkv(764, HQ, HKV, D, dtype, DEV, seed=3)
+    k[::5] *= 4.0  # a few dominant keys -> large max jumps between tiles
+    l = torch.tensor(lens, dtype=torch.int32, device=DEV)
+    out = _run(q, k, v, kc, vc, l, pt, bm, cu, HKV, PS)
+    ref = torch_prefill_fp32(q, k, v, torch.nan_to_num(kc), torch.nan_to_num(vc), l, pt, bm, cu, HKV, PS)
+    assert torch.isfinite(out).all()
+    assert (out.float() - ref).abs().max().item() <= ATOL[dtype]
