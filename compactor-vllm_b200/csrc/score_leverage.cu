@@ -1,0 +1,379 @@
+// Compactor pre-RoPE approximate leverage scores.
+//
+// Reference: compression/compactor.py:113-221 (torch: batched GEMM K.PHI,
+// python loops over chunks, cuSOLVER gesvda on the 48x48 Grams, second GEMM,
+// Triton z-score :224-269).  Here: ONE CTA per (chunk, kv head) does the whole
+// chain in shared memory, then one small launch z-scores each chunk.
+//
+//   X   = round16(K_h . PHI)                mma.sync, K rows straight from global
+//   Xc  = round16(X - round16(mean_t X))    per chunk
+//   G   = fp32(round16(Xc^T Xc)) + reg*I    mma.sync on the transposed sketch
+//   G   = V diag(lam) V^T                   parallel cyclic Jacobi, fp32, in smem
+//   u   = round16(Xc . round16(V |lam|^-1/2));  score = round16(sum_j round16(u_j^2))
+//
+// The reference keeps X, Xc, G, V S^-1/2, U and the row sums in K's 16-bit
+// dtype; rounding G entrywise perturbs it by far more than the
+// 5e-3 regulariser (it can even go indefinite: the SVD then yields |lam|), so
+// those rounding points are part of the reference's scores and are reproduced
+// here — an exact fp32 x^T G^-1 x only overlaps ~80 % with the reference's
+// kept set (tests/test_oracle_golden.py).  Work is ~170 KFLOP/token: latency
+// and launch count, not throughput, is what the fusion removes.
+#include "common.cuh"
+#include "mma.cuh"
+
+namespace cvllm {
+
+constexpr int kLevThreads = 256;
+constexpr int kSk = 48;            // sketch columns
+constexpr int kTokTile = 256;      // tokens per smem tile
+constexpr int kXtStride = kTokTile + 8;  // 16-bit elements per sketch row (pad: bank spread)
+constexpr int kJacobiSweeps = 10;
+
+struct LevParams {
+  const void* k;
+  int64_t k_stride_n, k_stride_h;  // elements
+  const int32_t* chunk_offsets;
+  const void* phi;  // [128, 48] 16-bit
+  float* raw;       // [N, HKV] fp32 (values already rounded to 16-bit)
+  int HKV;
+  float reg;
+};
+
+template <bool BF16>
+__device__ __forceinline__ float round16(float x) {
+  if constexpr (BF16) return __bfloat162float(__float2bfloat16_rn(x));
+  else return __half2float(__float2half_rn(x));
+}
+template <bool BF16>
+__device__ __forceinline__ uint16_t to16(float x) {
+  if constexpr (BF16) return __bfloat16_as_ushort(__float2bfloat16_rn(x));
+  else return __half_as_ushort(__float2half_rn(x));
+}
+template <bool BF16>
+__device__ __forceinline__ float from16(uint16_t x) {
+  if constexpr (BF16) return __uint_as_float((uint32_t)x << 16);
+  else return __half2float(__ushort_as_half(x));
+}
+
+struct LevSmem {
+  uint16_t phiT[kSk][128 + 32];       // PHI^T: sketch-major, d contiguous (+64 B pad: conflict-free LDS.128)
+  uint16_t xt[kSk][kXtStride];        // X^T tile: sketch-major, token contiguous
+  float g[kSk][kSk + 1];              // Gram -> diagonalised in place
+  float v[kSk][kSk + 1];              // eigenvectors (columns)
+  float sv[kSk][kSk];                 // round16(V |lam|^-1/2)
+  float colsum[kSk];
+  float mean[kSk];
+  float rot_c[kSk / 2], rot_s[kSk / 2];
+  int pair_p[kSk / 2], pair_q[kSk / 2];
+};
+
+// X^T tile for tokens [t0, t0+nt): xt[c][t] = round16(sum_d K[t][d] * PHI[d][c]) (optionally centred)
+template <bool BF16>
+__device__ __forceinline__ void sketch_tile(LevSmem& sm, const LevParams& p, int h, int tok0, int nt,
+                                            bool centre) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, r = lane >> 2, j = lane & 3;
+  const char* kb = reinterpret_cast<const char*>(p.k);
+  const int n_mt = (nt + 15) / 16;
+  for (int mt = warp; mt < n_mt; mt += kLevThreads / 32) {
+    const int t_lo = mt * 16 + r, t_hi = t_lo + 8;
+    auto krow = [&](int t) -> const char* {
+      return t < nt ? kb + ((int64_t)(tok0 + t) * p.k_stride_n + (int64_t)h * p.k_stride_h) * 2 : nullptr;
+    };
+    AFrag128 a;
+    a.load(krow(t_lo), krow(t_hi), j);
+#pragma unroll
+    for (int nn = 0; nn < kSk / 8; ++nn) {
+      float acc[4] = {0.f, 0.f, 0.f, 0.f};
+      const uint16_t* prow = sm.phiT[nn * 8 + r];
+#pragma unroll
+      for (int cc = 0; cc < 4; ++cc) {
+        const uint4 pb = *reinterpret_cast<const uint4*>(prow + (j + 4 * cc) * 8);
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+          const int ks = 2 * cc + half;
+          uint32_t a0, a1, a2, a3, b0, b1;
+          a.regs(ks, a0, a1, a2, a3);
+          bfrag_regs(pb, ks, b0, b1);
+          mma16816<BF16>(acc, a0, a1, a2, a3, b0, b1);
+        }
+      }
+      // acc: rows t_lo / t_hi, sketch cols nn*8 + 2j, +1
+      const int c0 = nn * 8 + 2 * j;
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        float x0 = round16<BF16>(acc[e]), x1 = round16<BF16>(acc[2 + e]);
+        if (centre) {
+          x0 = round16<BF16>(x0 - sm.mean[c0 + e]);
+          x1 = round16<BF16>(x1 - sm.mean[c0 + e]);
+        }
+        sm.xt[c0 + e][t_lo] = (t_lo < nt) ? to16<BF16>(x0) : 0;
+        sm.xt[c0 + e][t_hi] = (t_hi < nt) ? to16<BF16>(x1) : 0;
+      }
+    }
+  }
+}
+
+// grid (n_chunks, HKV)
+template <bool BF16>
+__global__ void __launch_bounds__(kLevThreads, 2) leverage_kernel(const LevParams p) {
+  extern __shared__ __align__(16) unsigned char lev_smem_raw[];
+  LevSmem& sm = *reinterpret_cast<LevSmem*>(lev_smem_raw);
+  const int ch = blockIdx.x, h = blockIdx.y;
+  const int c_beg = p.chunk_offsets[ch], c_len = p.chunk_offsets[ch + 1] - c_beg;
+  if (c_len <= 0) return;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+  // PHI^T into smem; zero accumulators
+  {
+    const uint16_t* phi = reinterpret_cast<const uint16_t*>(p.phi);
+    for (int i = tid; i < 128 * kSk; i += kLevThreads) {
+      const int d = i / kSk, c = i - d * kSk;
+      sm.phiT[c][d] = phi[i];
+    }
+    if (tid < kSk) sm.colsum[tid] = 0.f;
+    for (int i = tid; i < kSk * (kSk + 1); i += kLevThreads) (&sm.g[0][0])[i] = 0.f;
+  }
+  __syncthreads();
+
+  // ---- pass A: column means of X over the chunk ----
+  for (int t0 = 0; t0 < c_len; t0 += kTokTile) {
+    const int nt = min(kTokTile, c_len - t0);
+    sketch_tile<BF16>(sm, p, h, c_beg + t0, nt, false);
+    __syncthreads();
+    // 48 columns x 256 threads: warp w sums columns w, w+8, ...
+    for (int c = warp; c < kSk; c += kLevThreads / 32) {
+      float s = 0.f;
+      for (int t = lane; t < nt; t += 32) s += from16<BF16>(sm.xt[c][t]);
+      s = warp_sum(s);
+      if (lane == 0) sm.colsum[c] += s;
+    }
+    __syncthreads();
+  }
+  if (tid < kSk) sm.mean[tid] = round16<BF16>(sm.colsum[tid] / (float)c_len);
+  __syncthreads();
+
+  // ---- pass B: Gram of the centred sketch, G[i][j] = sum_t xc[t][i] xc[t][j] ----
+  // 6 x 6 tiles of 8 x 8; warp w owns (m-tile pair, n-tiles): use m16n8k16 with M = 16 sketch rows
+  for (int t0 = 0; t0 < c_len; t0 += kTokTile) {
+    const int nt = min(kTokTile, c_len - t0);
+    sketch_tile<BF16>(sm, p, h, c_beg + t0, nt, true);
+    __syncthreads();
+    // zero the padded token columns so partial k16 steps contribute nothing
+    const int nt16 = (nt + 15) & ~15;
+    for (int i = tid; i < kSk * (nt16 - nt); i += kLevThreads) {
+      const int c = i / (nt16 - nt), t = nt + i % (nt16 - nt);
+      sm.xt[c][t] = 0;
+    }
+    __syncthreads();
+    const int r = lane >> 2, j = lane & 3;
+    // 3 m-tiles (16 sketch rows) x 6 n-tiles (8 sketch cols) = 18 output tiles over 8 warps
+    for (int tile = warp; tile < 18; tile += kLevThreads / 32) {
+      const int mt = tile / 6, nn = tile - mt * 6;
+      float acc[4] = {0.f, 0.f, 0.f, 0.f};
+      const uint16_t* a_lo = sm.xt[mt * 16 + r];
+      const uint16_t* a_hi = sm.xt[mt * 16 + r + 8];
+      const uint16_t* b_r = sm.xt[nn * 8 + r];
+      for (int k0 = 0; k0 < nt16; k0 += 16) {
+        const uint32_t a0 = *reinterpret_cast<const uint32_t*>(a_lo + k0 + 2 * j);
+        const uint32_t a1 = *reinterpret_cast<const uint32_t*>(a_hi + k0 + 2 * j);
+        const uint32_t a2 = *reinterpret_cast<const uint32_t*>(a_lo + k0 + 8 + 2 * j);
+        const uint32_t a3 = *reinterpret_cast<const uint32_t*>(a_hi + k0 + 8 + 2 * j);
+        const uint32_t b0 = *reinterpret_cast<const uint32_t*>(b_r + k0 + 2 * j);
+        const uint32_t b1 = *reinterpret_cast<const uint32_t*>(b_r + k0 + 8 + 2 * j);
+        mma16816<BF16>(acc, a0, a1, a2, a3, b0, b1);
+      }
+      const int gi = mt * 16 + r, gj = nn * 8 + 2 * j;
+      sm.g[gi][gj] += acc[0];
+      sm.g[gi][gj + 1] += acc[1];
+      sm.g[gi + 8][gj] += acc[2];
+      sm.g[gi + 8][gj + 1] += acc[3];
+    }
+    __syncthreads();
+  }
+  // round the Gram to the 16-bit dtype (compactor.py:166,171,173), add the regulariser, V = I.
+  // Symmetrise from the upper triangle (staged through sv) so rounding cannot make G asymmetric.
+  for (int i = tid; i < kSk * kSk; i += kLevThreads) {
+    const int a = i / kSk, b = i - a * kSk;
+    sm.sv[a][b] = round16<BF16>(a <= b ? sm.g[a][b] : sm.g[b][a]);
+  }
+  __syncthreads();
+  for (int i = tid; i < kSk * kSk; i += kLevThreads) {
+    const int a = i / kSk, b = i - a * kSk;
+    sm.g[a][b] = sm.sv[a][b] + ((a == b) ? p.reg : 0.f);
+    sm.v[a][b] = (a == b) ? 1.f : 0.f;
+  }
+  __syncthreads();
+
+  // ---- parallel cyclic Jacobi: 24 disjoint (p,q) pairs per round, 47 rounds per sweep ----
+  for (int sweep = 0; sweep < kJacobiSweeps; ++sweep) {
+    for (int rnd = 0; rnd < kSk - 1; ++rnd) {
+      if (tid < kSk / 2) {
+        // round-robin tournament: position 0 fixed, the others rotate
+        const int n = kSk;
+        int a = (tid == 0) ? 0 : 1 + (tid - 1 + rnd) % (n - 1);
+        int b = 1 + (n - 2 - tid + rnd) % (n - 1);
+        if (tid == 0) b = 1 + (n - 2 + rnd) % (n - 1);
+        const int pp = min(a, b), qq = max(a, b);
+        const float app = sm.g[pp][pp], aqq = sm.g[qq][qq], apq = sm.g[pp][qq];
+        float c = 1.f, s = 0.f;
+        if (fabsf(apq) > 1e-30f) {
+          const float tau = (aqq - app) / (2.f * apq);
+          const float t = (tau >= 0.f ? 1.f : -1.f) / (fabsf(tau) + sqrtf(1.f + tau * tau));
+          c = rsqrtf(1.f + t * t);
+          s = t * c;
+        }
+        sm.rot_c[tid] = c; sm.rot_s[tid] = s; sm.pair_p[tid] = pp; sm.pair_q[tid] = qq;
+      }
+      __syncthreads();
+      // rows: G <- J^T G
+      for (int i = tid; i < (kSk / 2) * kSk; i += kLevThreads) {
+        const int pr = i / kSk, col = i - pr * kSk;
+        const int pp = sm.pair_p[pr], qq = sm.pair_q[pr];
+        const float c = sm.rot_c[pr], s = sm.rot_s[pr];
+        const float gp = sm.g[pp][col], gq = sm.g[qq][col];
+        sm.g[pp][col] = c * gp - s * gq;
+        sm.g[qq][col] = s * gp + c * gq;
+      }
+      __syncthreads();
+      // columns: G <- G J, V <- V J
+      for (int i = tid; i < (kSk / 2) * kSk; i += kLevThreads) {
+        const int pr = i / kSk, row = i - pr * kSk;
+        const int pp = sm.pair_p[pr], qq = sm.pair_q[pr];
+        const float c = sm.rot_c[pr], s = sm.rot_s[pr];
+        const float gp = sm.g[row][pp], gq = sm.g[row][qq];
+        sm.g[row][pp] = c * gp - s * gq;
+        sm.g[row][qq] = s * gp + c * gq;
+        const float vp = sm.v[row][pp], vq = sm.v[row][qq];
+        sm.v[row][pp] = c * vp - s * vq;
+        sm.v[row][qq] = s * vp + c * vq;
+      }
+      __syncthreads();
+    }
+  }
+  // SV = round16(V |lam|^-1/2)   (compactor.py:197: singular values of a symmetric G are |lam|)
+  for (int i = tid; i < kSk * kSk; i += kLevThreads) {
+    const int a = i / kSk, b = i - a * kSk;
+    sm.sv[a][b] = round16<BF16>(sm.v[a][b] * rsqrtf(fabsf(sm.g[b][b])));
+  }
+  __syncthreads();
+
+  // ---- pass C: score_t = round16(sum_j round16(round16(xc_t . sv_j)^2)) ----
+  for (int t0 = 0; t0 < c_len; t0 += kTokTile) {
+    const int nt = min(kTokTile, c_len - t0);
+    sketch_tile<BF16>(sm, p, h, c_beg + t0, nt, true);
+    __syncthreads();
+    for (int t = tid; t < nt; t += kLevThreads) {
+      float x[kSk];
+#pragma unroll
+      for (int c = 0; c < kSk; ++c) x[c] = from16<BF16>(sm.xt[c][t]);
+      float score = 0.f;
+#pragma unroll 4
+      for (int jc = 0; jc < kSk; jc += 4) {
+        float u0 = 0.f, u1 = 0.f, u2 = 0.f, u3 = 0.f;
+#pragma unroll
+        for (int c = 0; c < kSk; ++c) {
+          const float4 s4 = *reinterpret_cast<const float4*>(&sm.sv[c][jc]);
+          u0 = fmaf(x[c], s4.x, u0); u1 = fmaf(x[c], s4.y, u1);
+          u2 = fmaf(x[c], s4.z, u2); u3 = fmaf(x[c], s4.w, u3);
+        }
+        u0 = round16<BF16>(u0); u1 = round16<BF16>(u1); u2 = round16<BF16>(u2); u3 = round16<BF16>(u3);
+        score += round16<BF16>(u0 * u0) + round16<BF16>(u1 * u1) + round16<BF16>(u2 * u2) +
+                 round16<BF16>(u3 * u3);
+      }
+      p.raw[(int64_t)(c_beg + t0 + t) * p.HKV + h] = fmaxf(round16<BF16>(score), 0.f);
+    }
+    __syncthreads();
+  }
+}
+
+// grid (n_chunks): z-score a chunk over all heads (compactor.py:224-269) and cast to the output dtype
+template <bool BF16>
+__global__ void __launch_bounds__(256) leverage_finalize_kernel(const float* __restrict__ raw,
+                                                                const int32_t* __restrict__ chunk_offsets,
+                                                                void* __restrict__ out, int HKV, int normalize) {
+  const int ch = blockIdx.x;
+  const int beg = chunk_offsets[ch], len = chunk_offsets[ch + 1] - beg;
+  if (len <= 0) return;
+  const int total = len * HKV;
+  const float* src = raw + (int64_t)beg * HKV;
+  uint16_t* dst = reinterpret_cast<uint16_t*>(out) + (int64_t)beg * HKV;
+  __shared__ float s_red[2][8];
+  __shared__ float s_stat[2];
+  float mean = 0.f, invstd = 1.f;
+  if (normalize) {
+    float a1 = 0.f, a2 = 0.f;
+    for (int i = threadIdx.x; i < total; i += 256) {
+      const float v = src[i];
+      a1 += v;
+      a2 += v * v;
+    }
+    a1 = warp_sum(a1);
+    a2 = warp_sum(a2);
+    if ((threadIdx.x & 31) == 0) { s_red[0][threadIdx.x >> 5] = a1; s_red[1][threadIdx.x >> 5] = a2; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      float t1 = 0.f, t2 = 0.f;
+      for (int w = 0; w < 8; ++w) { t1 += s_red[0][w]; t2 += s_red[1][w]; }
+      const float cnt = (float)total;
+      const float m = t1 / cnt;
+      const float var = fmaxf(t2 / cnt - m * m, 0.f);
+      s_stat[0] = m;
+      s_stat[1] = 1.0f / sqrtf(var);
+    }
+    __syncthreads();
+    mean = s_stat[0];
+    invstd = s_stat[1];
+  }
+  for (int i = threadIdx.x; i < total; i += 256) {
+    float v = src[i];
+    if (normalize) v = (v - mean) * invstd;
+    dst[i] = to16<BF16>(v);
+  }
+}
+
+}  // namespace cvllm
+
+using namespace cvllm;
+
+extern "C" size_t cvllm_leverage_scores_workspace_bytes(int N, int HKV, int sketch, int n_chunks) {
+  (void)sketch; (void)n_chunks;
+  if (N <= 0 || HKV <= 0) return 256;
+  return (((size_t)N * HKV * sizeof(float)) + 255) & ~(size_t)255;
+}
+
+extern "C" int cvllm_leverage_scores(const void* k_pre, int64_t k_stride_n, int64_t k_stride_h,
+                                     const int32_t* chunk_offsets, int n_chunks, int max_chunk,
+                                     const void* phi, void* out_scores, int N, int HKV, int D, int sketch,
+                                     float regularizer, int normalize, int dtype, void* workspace,
+                                     size_t workspace_bytes, cvllm_stream_t stream) {
+  CVLLM_CHECK_ARG(N >= 0 && HKV > 0 && n_chunks >= 0 && max_chunk >= 0);
+  if (N == 0 || n_chunks == 0) return CVLLM_OK;
+  CVLLM_CHECK_ARG(k_pre && chunk_offsets && phi && out_scores && workspace);
+  CVLLM_CHECK_ARG(dtype == CVLLM_F16 || dtype == CVLLM_BF16);
+  CVLLM_CHECK_SUPPORTED(D == 128 && sketch == kSk);
+  CVLLM_CHECK_ALIGN(aligned16(k_pre) && k_stride_n % 8 == 0 && k_stride_h % 8 == 0);
+  CVLLM_CHECK_ARG(workspace_bytes >= cvllm_leverage_scores_workspace_bytes(N, HKV, sketch, n_chunks));
+  auto st = static_cast<cudaStream_t>(stream);
+  LevParams p;
+  p.k = k_pre; p.k_stride_n = k_stride_n; p.k_stride_h = k_stride_h; p.chunk_offsets = chunk_offsets;
+  p.phi = phi; p.raw = reinterpret_cast<float*>(workspace); p.HKV = HKV; p.reg = regularizer;
+  const size_t smem = sizeof(LevSmem);
+  static bool attr_set = false;
+  if (!attr_set) {
+    CVLLM_CHECK_CUDA(cudaFuncSetAttribute(leverage_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)smem));
+    CVLLM_CHECK_CUDA(cudaFuncSetAttribute(leverage_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)smem));
+    attr_set = true;
+  }
+  const dim3 grid(n_chunks, HKV);
+  if (dtype == CVLLM_BF16) {
+    leverage_kernel<true><<<grid, kLevThreads, smem, st>>>(p);
+    leverage_finalize_kernel<true><<<n_chunks, 256, 0, st>>>(p.raw, chunk_offsets, out_scores, HKV, normalize);
+  } else {
+    leverage_kernel<false><<<grid, kLevThreads, smem, st>>>(p);
+    leverage_finalize_kernel<false><<<n_chunks, 256, 0, st>>>(p.raw, chunk_offsets, out_scores, HKV, normalize);
+  }
+  CVLLM_CHECK_LAUNCH();
+  return CVLLM_OK;
+}
