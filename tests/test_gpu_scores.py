@@ -1,0 +1,215 @@
+"""Key scorers (Compactor leverage + chunk attention mass, SnapKV) vs the CPU oracle and the
+reference-generated goldens.
+
+Tolerance: finite entries |d| <= 2e-2 * max(1, |s|), +-inf pattern exact.  The
+leverage chain is ill-conditioned by construction in the reference (every intermediate lives in
+K's 16-bit dtype, and the z-score divides by a chunk's std), so next to the element tolerance it
+is judged the way it is used: overlap of the top-50 % kept set."""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+from compactor_vllm.compression.compactor import approximate_leverage_scores, non_causal_attn_scores
+from compactor_vllm.compression.snapkv import query_aware_key_scores
+from compactor_vllm.utils.arguments import make_phi
+from oracle import scoring as osc
+
+from conftest import load_golden
+from helpers import fused_qkv
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _close(out, ref, tol=2e-2):
+    out, ref = out.float().cpu(), ref.float().cpu()
+    assert torch.equal(torch.isinf(out), torch.isinf(ref)), "inf pattern differs"
+    assert torch.equal(torch.isnan(out), torch.isnan(ref)), "nan pattern differs"
+    fin = torch.isfinite(ref)
+    if fin.any():
+        d = (out[fin] - ref[fin]).abs() / ref[fin].abs().clamp_min(1.0)
+        assert d.max().item() <= tol, d.max().item()
+
+
+def _cu(lens):
+    return torch.tensor([0] + np.cumsum(lens).tolist(), dtype=torch.int32)
+
+
+# ------------------------------------------------------------------ chunk-local attention mass
+def test_chunk_scores_golden():
+    g = load_golden("chunk_scores")
+    q, k = g["q"].to(DEV), g["k"].to(DEV)
+    cu = g["cu_seqlens"].to(DEV)
+    lens = (g["cu_seqlens"][1:] - g["cu_seqlens"][:-1]).tolist()
+    raw = non_causal_attn_scores(q, k, None, cu, max(lens), g["chunk"], sm_scale=g["sm_scale"], normalize=False)
+    _close(raw, g["raw"])
+    full = non_causal_attn_scores(
+        q, k, None, cu, max(lens), g["chunk"], sm_scale=g["sm_scale"], normalize=True, context_lens=lens,
+        protected_first_tokens=g["prot_first"].tolist(), protected_last_tokens=g["prot_last"].tolist(),
+        accum_scores=g["accum"].to(DEV), accum_blending=0.5)
+    _close(full, g["full"])
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("lens,HQ,HKV", [([1], 32, 8), ([127, 129, 64], 32, 8), ([1000], 8, 1), ([300, 5], 16, 2),
+                                         ([513], 32, 8)])
+@pytest.mark.parametrize("sm_scale", [1.0, None])
+def test_chunk_scores_vs_oracle(dtype, lens, HQ, HKV, sm_scale):
+    N, D = sum(lens), 128
+    q, k, _ = fused_qkv(N, HQ, HKV, D, dtype, DEV, seed=N + HQ)
+    if sm_scale == 1.0:  # the engine's setting (compactor.py:51-58): keep logits in a sane range
+        q = (q * 0.3).contiguous()
+        k = (k * 0.3).contiguous()
+    cu = _cu(lens)
+    raw = non_causal_attn_scores(q, k, None, cu.to(DEV), max(lens), 128, sm_scale=sm_scale, normalize=False)
+    ref = osc.non_causal_attn_scores(q.cpu(), k.cpu(), cu, 128, sm_scale=sm_scale, normalize=False)
+    _close(raw, ref)
+    if min(lens) > 1:
+        g = torch.Generator().manual_seed(3)
+        accum = torch.randn((N, HKV), generator=g).to(dtype)
+        pf, pl = [4] * len(lens), [16] * len(lens)
+        out = non_causal_attn_scores(q, k, None, cu.to(DEV), max(lens), 128, sm_scale=sm_scale, normalize=True,
+                                     context_lens=lens, protected_first_tokens=pf, protected_last_tokens=pl,
+                                     accum_scores=accum.to(DEV), accum_blending=0.5)
+        ref = osc.non_causal_attn_scores(q.cpu(), k.cpu(), cu, 128, sm_scale=sm_scale, normalize=True,
+                                         context_lens=lens, protected_first_tokens=pf, protected_last_tokens=pl,
+                                         accum_scores=accum, accum_blending=0.5)
+        _close(out, ref)
+
+
+# ------------------------------------------------------------------------------------ SnapKV
+@pytest.mark.parametrize("seg", [32, 64])
+def test_snapkv_golden(seg):
+    g = load_golden(f"snapkv_seg{seg}")
+    cu = g["cu_seqlens"].to(DEV)
+    out = query_aware_key_scores(g["q"].to(DEV), g["k"].to(DEV), cu, cu, g["w"], pool_segment=g["pool_segment"])
+    ok = ~g["untouched_rows"]
+    _close(out.cpu()[ok], g["out"][ok])
+    assert (out.cpu()[~ok] == 0).all()
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("lens,HQ,HKV,w", [([40], 32, 8, 32), ([33, 500, 32, 10], 32, 8, 32), ([5000], 32, 8, 32),
+                                           ([2100, 300], 8, 1, 32), ([700], 16, 2, 8)])
+@pytest.mark.parametrize("seg", [64, 128])
+def test_snapkv_vs_oracle(dtype, lens, HQ, HKV, w, seg):
+    N, D = sum(lens), 128
+    q, k, _ = fused_qkv(N, HQ, HKV, D, dtype, DEV, seed=N + w)
+    cu = _cu(lens)
+    out = query_aware_key_scores(q, k, cu.to(DEV), cu.to(DEV), w, pool_segment=seg)
+    ref = osc.query_aware_key_scores(q.cpu(), k.cpu(), cu, cu, w, pool_segment=seg)
+    _close(out, ref)
+
+
+def test_snapkv_accumulates_in_place():
+    lens, HQ, HKV, w = [300], 32, 8, 32
+    q, k, _ = fused_qkv(sum(lens), HQ, HKV, 128, torch.bfloat16, DEV, seed=1)
+    cu = _cu(lens).to(DEV)
+    base = query_aware_key_scores(q, k, cu, cu, w)
+    acc = torch.ones_like(base)
+    ret = query_aware_key_scores(q, k, cu, cu, w, accum_scores=acc, accum_blending=0.25)
+    assert ret.data_ptr() == acc.data_ptr()  # the reference mutates its argument (snapkv.py:442-446)
+    fin = torch.isfinite(base)
+    assert torch.allclose(ret[fin], base[fin] + 0.25)
+
+
+# ---------------------------------------------------------------------------------- leverage
+def _structured_keys(N, H, D, dtype, seed):
+    """Low-rank + positional drift + noise: leverage scores with real spread (randn keys make them
+    near-uniform)."""
+    g = torch.Generator().manual_seed(seed)
+    basis = torch.randn((H, 12, D), generator=g)
+    coef = torch.randn((N, H, 12), generator=g) * torch.linspace(2.0, 0.2, 12)
+    pos = torch.linspace(0, 6.28, N)[:, None, None] * torch.ones(1, H, 1)
+    x = torch.einsum("nhr,hrd->nhd", coef, basis) + 0.5 * torch.sin(pos + torch.arange(D) * 0.1)
+    x = x + 0.3 * torch.randn((N, H, D), generator=g)
+    spikes = torch.randint(0, N, (max(1, N // 50),), generator=g)
+    x[spikes] += 3.0 * torch.randn((spikes.numel(), H, D), generator=g)
+    return x.to(dtype)
+
+
+def _overlap(a, b, frac=0.5):
+    k = max(1, int(a.numel() * frac))
+    ia = set(torch.topk(a.float().flatten(), k).indices.tolist())
+    ib = set(torch.topk(b.float().flatten(), k).indices.tolist())
+    return len(ia & ib) / k
+
+
+@pytest.mark.parametrize("name", ["leverage_bf16"])
+def test_leverage_golden(name):
+    g = load_golden(name)
+    lens = g["context_lens"].tolist()
+    raw = approximate_leverage_scores(g["keys"].to(DEV), lens, g["phi"].to(DEV), regularizer=g["regularizer"],
+                                      normalize=False, chunk_size=g["chunk_size"])
+    assert raw.dtype == g["keys"].dtype
+    d = (raw.float().cpu() - g["raw"].float()).abs()
+    assert d.max().item() <= 2e-2 * max(1.0, g["raw"].float().abs().max().item()), d.max().item()
+    norm = approximate_leverage_scores(g["keys"].to(DEV), lens, g["phi"].to(DEV), regularizer=g["regularizer"],
+                                       normalize=True, chunk_size=g["chunk_size"])
+    dn = (norm.float().cpu() - g["norm"].float()).abs().flatten()
+    assert dn.kthvalue(int(0.99 * dn.numel())).values.item() <= 5e-2
+    assert _overlap(norm.cpu(), g["norm"]) >= 0.98
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("lens,H,chunk", [([512], 8, 512), ([1300, 700], 8, 512), ([100, 49, 600], 2, 512),
+                                          ([2048], 4, 512), ([300], 8, 128)])
+def test_leverage_vs_oracle(dtype, lens, H, chunk):
+    N, D = sum(lens), 128
+    keys = _structured_keys(N, H, D, dtype, seed=N + H)
+    phi = make_phi(D, 48, dtype, "cpu")
+    raw = approximate_leverage_scores(keys.to(DEV), lens, phi.to(DEV), normalize=False, chunk_size=chunk)
+    ref = osc.approximate_leverage_scores(keys, lens, phi, normalize=False, chunk_size=chunk, emulate_dtype=True)
+    exact = osc.approximate_leverage_scores(keys, lens, phi, normalize=False, chunk_size=chunk, emulate_dtype=False)
+    d = (raw.float().cpu() - ref.float()).abs()
+    # both sides round every intermediate to 16 bits; they may round differently at each point, so
+    # the bound is a few ulps of the score range, and we must be no further from the exact fp32
+    # leverage score than the reference's own rounding chain is (x2 slack)
+    assert d.max().item() <= 3e-2, d.max().item()
+    e_mine = (raw.float().cpu() - exact.float()).abs().mean().item()
+    e_ref = (ref.float() - exact.float()).abs().mean().item()
+    assert e_mine <= 2.0 * e_ref + 1e-3, (e_mine, e_ref)
+    norm = approximate_leverage_scores(keys.to(DEV), lens, phi.to(DEV), normalize=True, chunk_size=chunk)
+    refn = osc.approximate_leverage_scores(keys, lens, phi, normalize=True, chunk_size=chunk, emulate_dtype=True)
+    _, chunk_lens = osc.split_into_chunks(lens, chunk)
+    if all(c >= 64 for c in chunk_lens):  # shorter chunks: leverage ~1 everywhere, z-score is noise
+        assert _overlap(norm.cpu(), refn) >= 0.97, _overlap(norm.cpu(), refn)
+        dn = (norm.float().cpu() - refn.float()).abs().flatten()
+        assert dn.kthvalue(max(1, int(0.99 * dn.numel()))).values.item() <= 0.1
+
+
+def test_leverage_one_token_chunk_is_nan():
+    """a 1-token tail chunk z-scores to 0/0 = NaN, which the ranking keeps first."""
+    lens, H = [513], 8
+    keys = _structured_keys(sum(lens), H, 128, torch.bfloat16, seed=5)
+    phi = make_phi(128, 48, torch.bfloat16, "cpu")
+    out = approximate_leverage_scores(keys.to(DEV), lens, phi.to(DEV), normalize=True, chunk_size=512)
+    assert torch.isnan(out[512]).all() and torch.isfinite(out[:512]).all()
+
+
+# ---------------------------------------------------------------- end-to-end Compactor scores
+def test_compactor_pipeline_kept_set_overlap():
+    """pre-RoPE leverage -> post-RoPE chunk scores (+0.5 blend, protection) -> top-50 % kept set:
+    overlap with the oracle's kept set, the quantity that matters downstream."""
+    lens, HQ, HKV, D, dtype = [1500, 600], 32, 8, 128, torch.bfloat16
+    N = sum(lens)
+    keys_pre = _structured_keys(N, HKV, D, dtype, seed=11)
+    q, k, _ = fused_qkv(N, HQ, HKV, D, dtype, "cpu", seed=12)
+    q, k = (q * 0.3).contiguous(), (k * 0.3).contiguous()
+    phi = make_phi(D, 48, dtype, "cpu")
+    cu = _cu(lens)
+    pf, pl = [16] * 2, [64] * 2
+    pre = approximate_leverage_scores(keys_pre.to(DEV), lens, phi.to(DEV), normalize=True, chunk_size=512)
+    out = non_causal_attn_scores(q.to(DEV), k.to(DEV), None, cu.to(DEV), max(lens), 128, sm_scale=1.0,
+                                 normalize=True, context_lens=lens, protected_first_tokens=pf,
+                                 protected_last_tokens=pl, accum_scores=pre, accum_blending=0.5)
+    pre0 = osc.approximate_leverage_scores(keys_pre, lens, phi, normalize=True, chunk_size=512)
+    ref = osc.non_causal_attn_scores(q, k, cu, 128, sm_scale=1.0, normalize=True, context_lens=lens,
+                                     protected_first_tokens=pf, protected_last_tokens=pl, accum_scores=pre0,
+                                     accum_blending=0.5)
+    assert torch.equal(torch.isinf(out.cpu()), torch.isinf(ref))
+    for b in range(2):
+        s, e = int(cu[b]), int(cu[b + 1])
+        assert _overlap(out.cpu()[s:e], ref[s:e]) >= 0.985
