@@ -1,0 +1,576 @@
+#!/usr/bin/env python
+"""Headline benchmark of the attention + KV-compression hot path (BASELINE.json's metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+        --master-port P bench.py --gpus N --steps K --warmup W
+
+Workload "M" (the "@32K, 50 % keep" row): per rank ONE 32768-token sequence,
+HQ=32 HKV=8 D=128 page=128 bf16, COMPACTOR compression keeping 50 % (first 16 / last 64 tokens
+protected), one transformer layer's hot path.  A *step* is one pass of that path over the
+sequence through the reference-shaped Python API:
+
+    scores = CompactorCompression.pre_rope_scoring(q, k_pre, v, ctx)     # leverage sketch, side stream
+    scores = CompactorCompression.post_rope_scoring(q, k, v, scores, ctx) # chunk attention mass + blend
+    out    = Attention.forward(q, k, v, scores)   # top-k select + page compaction on the side
+                                                  # stream, tcgen05 prefill attention on the main one
+
+`value` = algorithmic prefill attention FLOPs (causal half counted once, 4*D*HQ*L(L+1)/2) of all
+ranks / max-over-ranks step time, i.e. sparse-attention prefill TFLOP/s WITH compression in the
+step.  The other two numbers of the metric (decode HBM GB/s on the compacted cache, KV-compress
+Mtok/s) are measured in the same run and reported under "components".
+
+Ranks are independent sequences (weak scaling; the path has no collective).
+
+`--impl reference`: the reference has no CPU implementation; the timed CPU arm is
+the oracle/ restatement of the same path on the host cores, bounded sample.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import math
+import os
+import sys
+import threading
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+sys.path[:0] = [str(ROOT), str(ROOT / "compactor-vllm_b200")]
+
+import torch  # noqa: E402
+
+METRIC = "sparse attn prefill TFLOP/s, decode HBM GB/s, KV-compress Mtok/s @32K, 50% keep"
+HQ, HKV, D, PS = 32, 8, 128, 128
+SEQ = 32768
+RATIO, PROT_FIRST, PROT_LAST = 0.5, 16, 64
+SKETCH, LEV_CHUNK = 48, 512
+CPU_SAMPLE_TOKENS = 4096
+
+
+def prefill_flops(L: int, Lc: int = 0) -> float:
+    """4*D*HQ * (La*Lc + La(La+1)/2): QK^T + PV, 2 flops per MAC, only unmasked pairs."""
+    return 4.0 * D * HQ * (L * Lc + L * (L + 1) / 2)
+
+
+def peaks() -> dict:
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        d = json.loads(p.read_text())
+        return {"hbm": d["hbm_gbs"], "tensor_burst": d["bf16_tflops"],
+                "tensor_sustained": d.get("bf16_tflops_sustained", d["bf16_tflops"]), "src": "measured"}
+    return {"hbm": 6650.0, "tensor_burst": 1590.0, "tensor_sustained": 1400.0, "src": "fallback"}
+
+
+# --------------------------------------------------------------------------------------------
+# synthetic inputs (seeded; K has low-rank + positional structure so scores are not uniform)
+# --------------------------------------------------------------------------------------------
+def make_inputs(n_tok: int, device, dtype, seed: int):
+    g = torch.Generator(device=device).manual_seed(seed)
+    qkv = torch.randn((n_tok, (HQ + 2 * HKV) * D), generator=g, device=device, dtype=torch.float32)
+    basis = torch.randn((HKV, 12, D), generator=g, device=device)
+    coef = torch.randn((n_tok, HKV, 12), generator=g, device=device) * torch.linspace(2.0, 0.2, 12, device=device)
+    pos = torch.linspace(0, 50.0, n_tok, device=device)[:, None, None]
+    low = torch.einsum("nhr,hrd->nhd", coef, basis) + 0.5 * torch.sin(pos + torch.arange(D, device=device) * 0.1)
+    k_pre = (low + 0.3 * torch.randn((n_tok, HKV, D), generator=g, device=device)).to(dtype)
+    qkv = qkv.to(dtype)
+    kview = qkv[:, HQ * D:(HQ + HKV) * D].view(n_tok, HKV, D)
+    kview.add_((0.25 * low).to(dtype))
+    del basis, coef, low
+    return qkv, k_pre
+
+
+def split_qkv(qkv):
+    n = qkv.shape[0]
+    q = qkv[:, : HQ * D].view(n, HQ, D)
+    k = qkv[:, HQ * D:(HQ + HKV) * D].view(n, HKV, D)
+    v = qkv[:, (HQ + HKV) * D:].view(n, HKV, D)
+    return q, k, v
+
+
+# --------------------------------------------------------------------------------------------
+# clocks sampling during the timed region
+# --------------------------------------------------------------------------------------------
+class ClockSampler:
+    """Polls NVML (SM clock, power, clock-event reasons) every 10 ms while the timed region runs."""
+    REASONS = {0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown"}
+
+    def __init__(self, device_index: int):
+        self.samples, self.power, self.reasons, self.max_mhz = [], [], set(), None
+        self._stop = threading.Event()
+        self._thr = None
+        self._h = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            uuid = "GPU-" + str(torch.cuda.get_device_properties(device_index).uuid)
+            try:
+                self._h = pynvml.nvmlDeviceGetHandleByUUID(uuid.encode())
+            except Exception:
+                self._h = pynvml.nvmlDeviceGetHandleByIndex(device_index)
+            self._nv = pynvml
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            self._h = None
+
+    def _run(self):
+        nv, h = self._nv, self._h
+        while not self._stop.is_set():
+            try:
+                self.samples.append(float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)))
+                self.power.append(nv.nvmlDeviceGetPowerUsage(h) / 1000.0)
+                try:
+                    bits = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+                except Exception:
+                    bits = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                for bit, name in self.REASONS.items():
+                    if bits & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.01)
+
+    def start(self):
+        if self._h is None:
+            return
+        self._thr = threading.Thread(target=self._run, daemon=True)
+        self._thr.start()
+
+    def stop(self) -> dict:
+        self._stop.set()
+        if self._thr is not None:
+            self._thr.join(timeout=2.0)
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(s),
+                "power_w_max": max(self.power) if self.power else None}
+
+
+# --------------------------------------------------------------------------------------------
+# the GPU arm
+# --------------------------------------------------------------------------------------------
+class Workload:
+    """One rank's sequence, cache and the reference-shaped step."""
+
+    def __init__(self, device, n_tok: int, seed: int):
+        from compactor_vllm import _native as N
+        from compactor_vllm.compression.compactor import CompactorCompression
+        from compactor_vllm.compression.compression_config import CompressionMethod
+        from compactor_vllm.kv_cache.page_table import KVAllocationStatus, PagedKVCache
+        from compactor_vllm.layers.attention import Attention
+        from compactor_vllm.utils import arguments as A
+        from compactor_vllm.utils.context import CompressionContext
+
+        self.N = N
+        self.dev = device
+        self.dtype = torch.bfloat16
+        self.n_tok = n_tok
+        self.plugin = CompactorCompression
+        self.qkv, self.k_pre = make_inputs(n_tok, device, self.dtype, seed)
+        self.q, self.k, self.v = split_qkv(self.qkv)
+        n_lp = (n_tok + 2 * PS) // PS + 1
+        self.cache = PagedKVCache(num_layers=1, max_logical_pages_per_head=n_lp, num_pages=HKV * n_lp + 8,
+                                  page_size=PS, H_kv=HKV, head_dim=D, max_num_batches=2,
+                                  dtype=self.dtype, device=device)
+        self.slot = self.cache.new_batch()
+        st = self.cache.reserve_tokens(self.slot, n_tok)
+        assert st == KVAllocationStatus.SUCCESS, st
+        # scramble the physical pages (the allocator hands them out ascending): paging is exercised
+        pt = self.cache.page_table[0, self.slot]
+        n_used = int(self.cache.bh_num_pages[0, self.slot, 0])
+        flat = pt[:, :n_used].reshape(-1)
+        perm = torch.randperm(flat.numel(), generator=torch.Generator().manual_seed(seed)).to(device)
+        pt[:, :n_used] = flat[perm].view(HKV, n_used)
+        self.attn = Attention(HQ, D, 1.0 / math.sqrt(D), HKV)
+        kc, vc, ptab, bh = self.cache.layer_slices(0)
+        self.attn.k_cache, self.attn.v_cache, self.attn.page_table = kc, vc, ptab
+        self.attn.bh_seq_lens, self.attn.page_size = bh, PS
+        self.batch_mapping = torch.tensor([self.slot], dtype=torch.int32, device=device)
+        self.cu = torch.tensor([0, n_tok], dtype=torch.int32, device=device)
+        retain = A.tokens_to_retain([n_tok], [RATIO], [PROT_FIRST], [PROT_LAST], HKV)
+        self.retain = retain[0]
+        self.cctx = CompressionContext(
+            compression_method=CompressionMethod.COMPACTOR, compression_chunk_size=LEV_CHUNK,
+            batch_tokens_to_retain=torch.tensor(retain, dtype=torch.int32, device=device),
+            max_tokens_to_retain=A.max_tokens_to_retain([n_tok], HKV), context_lens=[n_tok],
+            PHI=A.make_phi(D, SKETCH, self.dtype, device), protected_first_tokens=[PROT_FIRST],
+            protected_last_tokens=[PROT_LAST])
+        self.store_stream = torch.cuda.Stream(device=device)
+        self.attn_events = []  # (start, end) around the prefill attention launch
+
+    # ---- context helpers -------------------------------------------------------------
+    def _prefill_ctx(self, compress: bool):
+        from compactor_vllm.utils.context import set_context
+        set_context(is_prefill=True, do_compression=compress, cu_seqlens_q=self.cu, cu_seqlens_k=self.cu,
+                    max_seqlen_q=self.n_tok, max_seqlen_k=self.n_tok, batch_mapping=self.batch_mapping,
+                    max_bh_len=0, compression_context=self.cctx if compress else None,
+                    STORE_STREAM=self.store_stream)
+
+    def reset_slot(self):
+        self.cache.bh_seq_lens[0, self.slot].zero_()
+
+    # ---- the step --------------------------------------------------------------------
+    def prefill_step(self, q=None, k=None, v=None, k_pre=None, compress=True):
+        from compactor_vllm.utils.context import get_context
+        q = self.q if q is None else q
+        k = self.k if k is None else k
+        v = self.v if v is None else v
+        k_pre = self.k_pre if k_pre is None else k_pre
+        self.reset_slot()
+        self._prefill_ctx(compress)
+        ctx = get_context()
+        scores = None
+        if compress:
+            scores = self.plugin.pre_rope_scoring(q, k_pre, v, ctx)
+            scores = self.plugin.post_rope_scoring(q, k, v, scores, ctx)
+        out = self.attn(q, k, v, scores)
+        torch.cuda.current_stream().wait_stream(self.store_stream)  # join: the step owns its stores
+        return out
+
+    def compress_only(self):
+        """score -> select -> store chain alone on one stream (KV-compress Mtok/s)."""
+        from compactor_vllm.compression.common import extract_and_store_top_kv
+        from compactor_vllm.compression.compactor import approximate_leverage_scores, non_causal_attn_scores
+        self.reset_slot()
+        c = self.cctx
+        pre = approximate_leverage_scores(self.k_pre, c.context_lens, c.PHI, normalize=True, chunk_size=LEV_CHUNK)
+        sc = non_causal_attn_scores(self.q, self.k, self.v, self.cu, self.n_tok, chunk_size=128, sm_scale=1.0,
+                                    normalize=True, accum_scores=pre, context_lens=c.context_lens,
+                                    protected_first_tokens=c.protected_first_tokens,
+                                    protected_last_tokens=c.protected_last_tokens, accum_blending=0.5)
+        lens = self.cache.bh_seq_lens[0].index_select(0, self.batch_mapping).contiguous()
+        extract_and_store_top_kv(sc, self.cu, self.n_tok, c.max_tokens_to_retain, HKV, self.k, self.v,
+                                 c.batch_tokens_to_retain, self.attn.page_table, self.batch_mapping, lens,
+                                 self.attn.k_cache, self.attn.v_cache, PS, PAD_TO_PAGE_SIZE=True)
+        self.cache.bh_seq_lens[0].index_copy_(0, self.batch_mapping.long(), lens)
+
+
+def install_attention_timer(w: Workload):
+    """Record CUDA events on the launching stream around the prefill attention call."""
+    import compactor_vllm.layers.attention as LA
+    inner = LA.causal_sparse_varlen_with_cache
+    if getattr(inner, "_bench_timed", False):
+        return
+
+    def timed(*a, **kw):
+        s = torch.cuda.Event(enable_timing=True)
+        e = torch.cuda.Event(enable_timing=True)
+        s.record()
+        out = inner(*a, **kw)
+        e.record()
+        w.attn_events.append((s, e))
+        return out
+
+    timed._bench_timed = True
+    LA.causal_sparse_varlen_with_cache = timed
+
+
+def time_loop(fn, iters: int, flush=None) -> float:
+    """Average ms per call with CUDA events around each call (L2 flushed before each if given)."""
+    tot = 0.0
+    for _ in range(iters):
+        if flush is not None:
+            flush.zero_()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        fn()
+        b.record()
+        b.synchronize()
+        tot += a.elapsed_time(b)
+    return tot / iters
+
+
+def decode_bench(device, dtype, B: int, lens_bh: torch.Tensor, iters: int, flush, seed: int):
+    """decode_store_kv + head_sparse_decode_attention on a synthetic compacted cache; returns
+    (ms per step, algorithmic bytes per step)."""
+    from compactor_vllm.attention.sparse_decode_kernel import head_sparse_decode_attention
+    from compactor_vllm.kv_cache.store_kv_cache import decode_store_kv
+    g = torch.Generator().manual_seed(seed)
+    nlp = int((int(lens_bh.max()) + iters + 8 + PS - 1) // PS)
+    n_pages = (B + 1) * HKV * nlp
+    pt = torch.randperm(n_pages, generator=g).to(torch.int32).view(B + 1, HKV, nlp).to(device)
+    kc = torch.randn((n_pages * PS, D), device=device, dtype=dtype)
+    vc = torch.randn((n_pages * PS, D), device=device, dtype=dtype)
+    bm = torch.arange(1, B + 1, dtype=torch.int32, device=device)
+    lens = lens_bh.to(torch.int32).to(device).contiguous()
+    q = torch.randn((B, HQ, D), device=device, dtype=dtype)
+    kn = torch.randn((B, HKV, D), device=device, dtype=dtype)
+    vn = torch.randn((B, HKV, D), device=device, dtype=dtype)
+
+    def step():
+        decode_store_kv(key=kn, value=vn, batch_mapping=bm, bh_lens=lens, page_table=pt, k_cache=kc,
+                        v_cache=vc, PAGE_SIZE=PS)
+        return head_sparse_decode_attention(q, kc, vc, lens, pt, bm, HKV, PS)
+
+    for _ in range(3):
+        step()
+    torch.cuda.synchronize()
+    ms = time_loop(step, iters, flush)
+    rows = int(lens_bh.sum()) + B * HKV * (3 + iters // 2)
+    nbytes = rows * D * 2 * 2 + B * HQ * D * 2 * 2 + B * HKV * D * 2 * 2 * 2
+    return ms, nbytes
+
+
+def cpu_sample(n_tok: int, threads: int):
+    """The oracle's restatement of one step on `n_tok` tokens; returns (seconds, prefill flops)."""
+    import oracle.attention as oa
+    import oracle.scoring as osc
+    import oracle.selection as osel
+    torch.set_num_threads(threads)
+    qkv, k_pre = make_inputs(n_tok, "cpu", torch.bfloat16, 7)
+    q, k, v = split_qkv(qkv)
+    from compactor_vllm.utils import arguments as A
+    phi = A.make_phi(D, SKETCH, torch.bfloat16, "cpu")
+    n_lp = n_tok // PS + 2
+    pt = torch.arange(2 * HKV * n_lp, dtype=torch.int32).view(2, HKV, n_lp)
+    kc = torch.zeros((2 * HKV * n_lp * PS, D), dtype=torch.bfloat16)
+    vc = torch.zeros_like(kc)
+    lens = torch.zeros((1, HKV), dtype=torch.int32)
+    bm = torch.tensor([1], dtype=torch.int32)
+    cu = torch.tensor([0, n_tok], dtype=torch.int32)
+    retain = A.tokens_to_retain([n_tok], [RATIO], [PROT_FIRST], [PROT_LAST], HKV)
+    t0 = time.perf_counter()
+    pre = osc.approximate_leverage_scores(k_pre, [n_tok], phi, normalize=True, chunk_size=LEV_CHUNK)
+    sc = osc.non_causal_attn_scores(q, k, cu, 128, sm_scale=1.0, normalize=True, context_lens=[n_tok],
+                                    protected_first_tokens=[PROT_FIRST], protected_last_tokens=[PROT_LAST],
+                                    accum_scores=pre, accum_blending=0.5)
+    out = oa.prefill_attention(q, k, v, kc, vc, lens, pt, bm, cu, HKV, PS)
+    osel.extract_and_store_top_kv(sc, cu, n_tok, n_tok * HKV, HKV, k, v, retain, pt, bm, lens, kc, vc, PS,
+                                  pad=True)
+    dt = time.perf_counter() - t0
+    assert torch.isfinite(out).all()
+    return dt, prefill_flops(n_tok)
+
+
+def run_reference_arm(args, rank: int, world: int):
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    n = CPU_SAMPLE_TOKENS
+    n_warm = max(0, min(args.warmup, 2))
+    for i in range(n_warm):
+        dt, _ = cpu_sample(n, threads)
+        if i == 0 and dt < 2.5:
+            n = 4 * CPU_SAMPLE_TOKENS
+    ts, t_begin = [], time.perf_counter()
+    for _ in range(max(1, args.steps)):
+        dt, fl = cpu_sample(n, threads)
+        ts.append(dt)
+        if time.perf_counter() - t_begin > 150.0:  # keep the whole arm within a few minutes
+            break
+    dt = sum(ts) / len(ts)
+    val = fl / dt / 1e12
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": "TFLOP/s", "n_gpus": args.gpus,
+        "steps": len(ts), "warmup": n_warm, "ms_per_step": dt * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(),
+        "cpu_baseline": {"value": val, "unit": "TFLOP/s", "cores": threads, "kind": "port",
+                         "sample": f"{n}-token slice of the workload (same heads, same compression), "
+                                   "oracle/ restatement: the reference has no CPU path (SURVEY 8d)"},
+        "e2e": {"value": val, "unit": "TFLOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config() -> dict:
+    return {
+        "workload": f"M: 1 x {SEQ}-token sequence per rank, HQ={HQ} HKV={HKV} D={D} page={PS} bf16, "
+                    f"COMPACTOR keep {int(RATIO * 100)}% (first {PROT_FIRST}/last {PROT_LAST} protected), "
+                    "one layer's hot path per step",
+        "l2": "prefill inputs (470 MB) exceed the 126 MB L2; decode iterations flush L2 (256 MB write)",
+        "parallelism": "independent sequences per rank, no collective in the path",
+    }
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--seq", type=int, default=SEQ, help=argparse.SUPPRESS)
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-extras", action="store_true", help="only the headline step (for ncu runs)")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", 0))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    if args.impl == "reference":
+        run_reference_arm(args, rank, world)
+        return
+    args.warmup = max(args.warmup, 3)
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (there is no CPU fallback)"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x: float) -> float:
+        if dist is None:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(x: float) -> float:
+        if dist is None:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    from compactor_vllm import _native as N
+    lib = N.lib()
+    n_tok = args.seq
+    w = Workload(dev, n_tok, seed=1234 + rank)
+    install_attention_timer(w)
+    pk = peaks()
+    flops = prefill_flops(n_tok)
+
+    # ---------------- headline: K timed steps ----------------
+    for _ in range(args.warmup):
+        w.prefill_step()
+    barrier()
+    w.attn_events.clear()
+    sampler = ClockSampler(local)
+    barrier()
+    sampler.start()
+    launches0 = lib.cvllm_launch_count()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(args.steps):
+        w.prefill_step()
+    ev1.record()
+    barrier()
+    launches = lib.cvllm_launch_count() - launches0
+    ms_step = max_over_ranks(ev0.elapsed_time(ev1) / args.steps)
+    attn_ms = sum(s.elapsed_time(e) for s, e in w.attn_events) / max(1, len(w.attn_events))
+    clocks = sampler.stop()
+    value = flops * world / (ms_step * 1e-3) / 1e12
+    total_launches = int(sum_over_ranks(float(launches)))
+
+    # kept pairs after the last step (for the decode leg and the report)
+    kept_bh = w.cache.bh_seq_lens[0, w.slot].cpu()
+    kept_pairs = int(kept_bh.sum())
+
+    comps = {"prefill_tflops_with_compression": value, "prefill_attn_kernel_ms": attn_ms,
+             "kept_pairs": kept_pairs, "retain_budget": w.retain}
+    roof_dec = None
+    e2e = None
+    cpu_base = None
+    if not args.no_extras:
+        # ---------------- attention alone (no compression in the step) ----------------
+        for _ in range(2):
+            w.prefill_step(compress=False)
+        torch.cuda.synchronize()
+        ms_plain = max_over_ranks(time_loop(lambda: w.prefill_step(compress=False), max(3, args.steps // 2)))
+        comps["prefill_tflops_no_compression"] = flops * world / (ms_plain * 1e-3) / 1e12
+        comps["compression_added_pct"] = 100.0 * (ms_step - ms_plain) / ms_plain
+
+        # ---------------- compression chain alone ----------------
+        for _ in range(2):
+            w.compress_only()
+        torch.cuda.synchronize()
+        ms_comp = max_over_ranks(time_loop(w.compress_only, max(3, args.steps // 2)))
+        comps["compress_mtok_s"] = n_tok * world / (ms_comp * 1e-3) / 1e6
+        comps["compress_ms"] = ms_comp
+        comp_bytes = n_tok * (2048 + 8192 + 2048 + HKV * 4 * 4) + kept_pairs * 1024
+        comps["compress_implied_gbs"] = comp_bytes / (ms_comp * 1e-3) / 1e9
+
+        # ---------------- decode on the compacted shape ----------------
+        flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
+        it = 40
+        ms_d1, by_d1 = decode_bench(dev, torch.bfloat16, 1, kept_bh.view(1, HKV), it, flush, 5)
+        ms_d1 = max_over_ranks(ms_d1)
+        comps["decode_gbs"] = by_d1 * world / (ms_d1 * 1e-3) / 1e9
+        comps["decode_us"] = ms_d1 * 1e3
+        g = torch.Generator().manual_seed(3)
+        lens16 = (torch.rand((16, HKV), generator=g) * 1.0 + 0.5) * 10240  # ragged, mean 10240 (cfg 3: 40K x 25 %)
+        ms_d16, by_d16 = decode_bench(dev, torch.bfloat16, 16, lens16.long(), it, flush, 6)
+        ms_d16 = max_over_ranks(ms_d16)
+        comps["decode_b16_gbs"] = by_d16 * world / (ms_d16 * 1e-3) / 1e9
+        comps["decode_b16_us"] = ms_d16 * 1e3
+        roof_dec = {"bound": "hbm", "achieved": by_d16 / (ms_d16 * 1e-3) / 1e9, "peak": pk["hbm"], "unit": "GB/s",
+                    "frac": by_d16 / (ms_d16 * 1e-3) / 1e9 / pk["hbm"], "traffic": None,
+                    "kernel": "decode_attn_kernel (B=16 ragged, mean 10240 rows/head)", "peak_src": pk["src"]}
+        del flush
+
+        # ---------------- end to end: pinned host buffers in, host out ----------------
+        h_qkv = torch.empty(w.qkv.shape, dtype=w.qkv.dtype).pin_memory()
+        h_kpre = torch.empty(w.k_pre.shape, dtype=w.k_pre.dtype).pin_memory()
+        h_qkv.copy_(w.qkv)
+        h_kpre.copy_(w.k_pre)
+        h_out = torch.empty((n_tok, HQ, D), dtype=w.dtype).pin_memory()
+        d_qkv = torch.empty_like(w.qkv)
+        d_kpre = torch.empty_like(w.k_pre)
+
+        def e2e_step():
+            d_kpre.copy_(h_kpre, non_blocking=True)
+            d_qkv.copy_(h_qkv, non_blocking=True)
+            q, k, v = split_qkv(d_qkv)
+            out = w.prefill_step(q, k, v, d_kpre)
+            h_out.copy_(out, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+
+        for _ in range(2):
+            e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        n_e2e = max(3, args.steps // 2)
+        for _ in range(n_e2e):
+            e2e_step()
+        barrier()
+        e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3 / n_e2e)
+        e2e = {"value": flops * world / (e2e_ms * 1e-3) / 1e12, "unit": "TFLOP/s",
+               "h2d_bytes_per_step": int(h_qkv.numel() * 2 + h_kpre.numel() * 2),
+               "d2h_bytes_per_step": int(h_out.numel() * 2), "ms_per_step": e2e_ms,
+               "api": "CompactorCompression.pre/post_rope_scoring + Attention.forward, pinned host q/k/v in, out back"}
+        del h_qkv, h_kpre, h_out, d_qkv, d_kpre
+
+        # ---------------- CPU baseline (rank 0, N=1 only) ----------------
+        if rank == 0 and world == 1 and not args.no_cpu:
+            threads = os.cpu_count() or 1
+            n_cpu = CPU_SAMPLE_TOKENS
+            dt, fl = cpu_sample(n_cpu, threads)
+            if dt < 2.5:  # fast host: take the 16K slice so the sample is ~10-30 s of CPU work
+                n_cpu = 4 * CPU_SAMPLE_TOKENS
+                dt, fl = cpu_sample(n_cpu, threads)
+            cpu_base = {"value": fl / dt / 1e12, "unit": "TFLOP/s", "cores": threads, "kind": "port",
+                        "sample": f"one step on a {n_cpu}-token slice (same heads and compression), "
+                                  f"oracle/ fp32 restatement, {dt:.1f} s"}
+
+    if rank == 0:
+        roof = {"bound": "tensor", "achieved": flops / (attn_ms * 1e-3) / 1e12, "peak": pk["tensor_sustained"],
+                "unit": "TFLOP/s", "frac": flops / (attn_ms * 1e-3) / 1e12 / pk["tensor_sustained"],
+                "traffic": None, "kernel": "prefill_attn_kernel<bf16>",
+                "peak_src": pk["src"] + " (sustained cuBLAS bf16: kernel timed inside a long step)",
+                "frac_of_burst_peak": flops / (attn_ms * 1e-3) / 1e12 / pk["tensor_burst"]}
+        prof = ROOT / "profiles" / "r01_prefill_traffic.json"
+        if prof.exists():
+            try:
+                roof["traffic"] = json.loads(prof.read_text()).get("dram_bytes_per_launch")
+            except Exception:
+                pass
+        line = {
+            "metric": METRIC, "value": value, "unit": "TFLOP/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "config": workload_config(),
+            "components": comps, "roofline": roof, "roofline_decode": roof_dec, "cpu_baseline": cpu_base,
+            "e2e": e2e, "gpu_launches": total_launches, "clocks": clocks,
+        }
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

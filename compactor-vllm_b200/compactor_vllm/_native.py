@@ -21,6 +21,7 @@ _i, _i64, _f, _p, _sz, _u32 = C.c_int, C.c_int64, C.c_float, C.c_void_p, C.c_siz
 _SIGNATURES = {
     "cvllm_abi_version": (C.c_int, []),
     "cvllm_last_error": (C.c_char_p, []),
+    "cvllm_launch_count": (C.c_uint64, []),
     "cvllm_decode_store_kv": (_i, [_p, _p, _i64, _i64, _i64, _i64, _p, _p, _p, _p, _p,
                                    _i, _i, _i, _i, _i, _i, _i, _p]),
     "cvllm_prefill_store_all": (_i, [_p, _p, _i64, _i64, _i64, _i64, _p, _p, _p, _p, _p, _p,

@@ -50,11 +50,20 @@ void set_last_error(const char* msg);
     }                                                                          \
   } while (0)
 
-#define CVLLM_CHECK_LAUNCH() CVLLM_CHECK_CUDA(cudaPeekAtLastError())
+// every kernel launch of the library is counted (cvllm_launch_count) so callers can state how
+// many of OUR kernels ran inside a timed region
+void note_launches(int n);
+#define CVLLM_CHECK_LAUNCHES(n)                                                \
+  do {                                                                         \
+    ::cvllm::note_launches(n);                                                 \
+    CVLLM_CHECK_CUDA(cudaPeekAtLastError());                                   \
+  } while (0)
+#define CVLLM_CHECK_LAUNCH() CVLLM_CHECK_LAUNCHES(1)
 
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 int sm_count();
+uint64_t launches();
 
 // ---------------------------------------------------------------------------
 // small device helpers

@@ -1,5 +1,6 @@
 // Host-side runtime glue: error string, device properties, TMA descriptor
 // encoding through the driver entry point (no link-time libcuda dependency).
+#include <atomic>
 #include <mutex>
 #include <string.h>
 
@@ -14,6 +15,10 @@ void set_last_error(const char* msg) {
   strncpy(g_last_error, msg ? msg : "", sizeof(g_last_error) - 1);
   g_last_error[sizeof(g_last_error) - 1] = 0;
 }
+
+static std::atomic<uint64_t> g_launches{0};
+void note_launches(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
+uint64_t launches() { return g_launches.load(std::memory_order_relaxed); }
 
 int sm_count() {
   static int cached[64] = {0};
@@ -82,3 +87,4 @@ int make_tmap_16b(CUtensorMap* map, const void* base, int rank, const uint64_t* 
 
 extern "C" int cvllm_abi_version(void) { return CVLLM_ABI_VERSION; }
 extern "C" const char* cvllm_last_error(void) { return cvllm::g_last_error; }
+extern "C" uint64_t cvllm_launch_count(void) { return cvllm::launches(); }

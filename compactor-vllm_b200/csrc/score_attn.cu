@@ -553,6 +553,6 @@ extern "C" int cvllm_snapkv_scores(const void* q, const void* k, int64_t q_strid
     snap_stats_kernel<false><<<g1, kScThreads, kScSmem, st>>>(p);
     snap_scores_kernel<false><<<g2, kScThreads, kScSmem, st>>>(p);
   }
-  CVLLM_CHECK_LAUNCH();
+  CVLLM_CHECK_LAUNCHES(2);
   return CVLLM_OK;
 }

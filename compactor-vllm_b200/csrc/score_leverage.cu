@@ -374,6 +374,6 @@ extern "C" int cvllm_leverage_scores(const void* k_pre, int64_t k_stride_n, int6
     leverage_kernel<false><<<grid, kLevThreads, smem, st>>>(p);
     leverage_finalize_kernel<false><<<n_chunks, 256, 0, st>>>(p.raw, chunk_offsets, out_scores, HKV, normalize);
   }
-  CVLLM_CHECK_LAUNCH();
+  CVLLM_CHECK_LAUNCHES(2);
   return CVLLM_OK;
 }

@@ -492,7 +492,7 @@ extern "C" int cvllm_rank_scores(const float* scores, int64_t s_stride_n, const 
     sort_scan_kernel<<<B, kSelThreads, 0, st>>>(hist, tiles);
     sort_scatter_kernel<<<dim3(tiles, B), kSortThreads, 0, st>>>(keys0, idx0, keys1, idx1, total, tiles,
                                                                   shift, hist);
-    CVLLM_CHECK_LAUNCH();
+    CVLLM_CHECK_LAUNCHES(3);
     uint32_t* t = keys0; keys0 = keys1; keys1 = t;
     t = idx0; idx0 = idx1; idx1 = t;
   }
@@ -603,7 +603,7 @@ extern "C" int cvllm_prefill_store_topk_idx(
                                                             cu_seqlens_k, batch_mapping, bh_lens, cnt,
                                                             HKV, PS, reserved_batch, keep);
     }
-    CVLLM_CHECK_LAUNCH();
+    CVLLM_CHECK_LAUNCHES(pad_to_page ? 2 : 1);
   }
   compact_head_kernel<1><<<dim3(HKV, B), kSelThreads, 0, st>>>(nullptr, 0, keep, cu_seqlens_k,
                                                                batch_mapping, nullptr, bh_lens, HKV,

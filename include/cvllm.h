@@ -47,6 +47,9 @@ typedef void* cvllm_stream_t;
 /* ABI version + last CUDA error string (host, static storage). */
 int cvllm_abi_version(void);
 const char* cvllm_last_error(void);
+/* Number of kernels this library has launched in this process (monotonic).
+ * Lets a caller report how many of its kernels ran inside a timed region. */
+uint64_t cvllm_launch_count(void);
 
 /* ------------------------------------------------------------------------
  * Store path
