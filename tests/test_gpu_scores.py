@@ -164,8 +164,11 @@ def test_leverage_golden(name):
     for L in chunk_lens:
         full[off:off + L] = L >= 48
         off += L
-    dn = (norm.float().cpu() - g["norm"].float()).abs()[full].flatten()
-    assert dn.kthvalue(int(0.99 * dn.numel())).values.item() <= 5e-2
+    # z-scores live in 16-bit storage on both sides: the bound is relative to the
+    # score magnitude (2 bf16 ulps at |z| in [4, 8) is already 0.06)
+    ref_n = g["norm"].float()[full].flatten()
+    dn = (norm.float().cpu()[full].flatten() - ref_n).abs() / ref_n.abs().clamp_min(1.0)
+    assert dn.kthvalue(int(0.99 * dn.numel())).values.item() <= 5e-2, dn.max().item()
     assert _overlap(norm.cpu()[full], g["norm"][full]) >= 0.98
 
 
