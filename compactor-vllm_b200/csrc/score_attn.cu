@@ -63,124 +63,180 @@ struct ChunkParams {
   const int32_t* cu;
   float* raw;        // [N, HKV] column sums (pre z-score)
   float* partials;   // [B, max_chunks, HKV, 2] (sum, sumsq) of raw per CTA
-  int HQ, HKV, G, chunk, max_chunks;
+  int B, HQ, HKV, G, chunk, max_chunks, n_ci;  // n_ci = chunks of the longest sequence
   float scale_log2;
 };
 
-// grid (max_chunks, HKV, B)
+// async copy of a [<=128 keys x 128 d] tile into padded smem (rows >= n_keys zero-filled)
+__device__ __forceinline__ void stage_k_tile_async(unsigned char* s_k, const char* k_base,
+                                                   int64_t k_stride_bytes, int n_keys) {
+  for (int idx = threadIdx.x; idx < kKeyTile * 16; idx += blockDim.x) {
+    const int r = idx >> 4, c = idx & 15;
+    const uint32_t dst = static_cast<uint32_t>(__cvta_generic_to_shared(s_k + r * kKRowBytes + c * 16));
+    const bool ok = r < n_keys;
+    const char* src = k_base + (int64_t)(ok ? r : 0) * k_stride_bytes + c * 16;
+    const int nbytes = ok ? 16 : 0;  // src-size 0: the 16 destination bytes are zero-filled
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(nbytes) : "memory");
+  }
+  asm volatile("cp.async.commit_group;" ::: "memory");
+}
+
+// Persistent: grid = min(items, #SM); item = (b, kv head, chunk).  The K tile of the NEXT item is
+// in flight (cp.async, second smem buffer) and the Q fragments of the next m-tile are in
+// registers while the current one is multiplied: the kernel is otherwise latency-bound (one
+// 8-warp CTA per SM, 12 KB between consecutive query tokens).
 template <bool BF16>
 __global__ void __launch_bounds__(kScThreads, 1) chunk_scores_kernel(const ChunkParams p) {
-  extern __shared__ __align__(16) unsigned char s_k[];  // [128][kKRowBytes]
+  extern __shared__ __align__(16) unsigned char s_kbuf[];  // 2 x [128][kKRowBytes]
   __shared__ float s_col[kScThreads / 32][kKeyTile];
-  const int ci = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
-  const int seq_beg = p.cu[b], seq_end = p.cu[b + 1];
-  const int cs = seq_beg + ci * p.chunk;
-  if (cs >= seq_end) return;
-  const int M = min(p.chunk, seq_end - cs);  // tokens (= keys) in this chunk
+  __shared__ float s_red[2][kScThreads / 32];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, r = lane >> 2, j = lane & 3;
   const int G = p.G;
-
-  stage_k_tile(s_k, reinterpret_cast<const char*>(p.k) + ((int64_t)cs * p.k_stride_n + h * 128) * 2,
-               p.k_stride_n * 2, M);
-  __syncthreads();
-
-  // rows = (token, g): row R -> token R / G, query head h*G + R % G
-  const int n_rows = M * G;
-  const int n_mt = (n_rows + 15) / 16;
-  float colacc[16][2];
-#pragma unroll
-  for (int nt = 0; nt < 16; ++nt) colacc[nt][0] = colacc[nt][1] = 0.f;
-
+  const int total = p.B * p.HKV * p.n_ci;
   const char* qb = reinterpret_cast<const char*>(p.q);
-  for (int mt = warp; mt < n_mt; mt += kScThreads / 32) {
-    const int R0 = mt * 16 + r, R1 = R0 + 8;
+
+  // item -> (b, h, ci); returns false when the chunk lies beyond its sequence
+  auto decode = [&](int idx, int& b, int& h, int& ci, int& cs, int& M) -> bool {
+    ci = idx % p.n_ci;
+    const int t = idx / p.n_ci;
+    h = t % p.HKV;
+    b = t / p.HKV;
+    const int seq_beg = p.cu[b], seq_end = p.cu[b + 1];
+    cs = seq_beg + ci * p.chunk;
+    M = min(p.chunk, seq_end - cs);
+    return cs < seq_end;
+  };
+  auto next_valid = [&](int idx) -> int {
+    int b, h, ci, cs, M;
+    while (idx < total && !decode(idx, b, h, ci, cs, M)) idx += gridDim.x;
+    return idx;
+  };
+  auto prefetch = [&](int idx, int buf) {
+    int b, h, ci, cs, M;
+    decode(idx, b, h, ci, cs, M);
+    stage_k_tile_async(s_kbuf + buf * (kKeyTile * kKRowBytes),
+                       reinterpret_cast<const char*>(p.k) + ((int64_t)cs * p.k_stride_n + h * 128) * 2,
+                       p.k_stride_n * 2, M);
+  };
+
+  int cur = next_valid(blockIdx.x);
+  int buf = 0;
+  if (cur < total) prefetch(cur, 0);
+  while (cur < total) {
+    const int nxt = next_valid(cur + gridDim.x);
+    if (nxt < total) {
+      prefetch(nxt, buf ^ 1);
+      asm volatile("cp.async.wait_group 1;" ::: "memory");
+    } else {
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+    }
+    __syncthreads();
+    const unsigned char* s_k = s_kbuf + buf * (kKeyTile * kKRowBytes);
+    int b, h, ci, cs, M;
+    decode(cur, b, h, ci, cs, M);
+
+    // rows = (token, g): row R -> token R / G, query head h*G + R % G
+    const int n_rows = M * G;
+    const int n_mt = (n_rows + 15) / 16;
+    float colacc[16][2];
+#pragma unroll
+    for (int nt = 0; nt < 16; ++nt) colacc[nt][0] = colacc[nt][1] = 0.f;
     auto qrow = [&](int R) -> const char* {
       if (R >= n_rows) return nullptr;
       const int tok = R / G, g = R - tok * G;
       return qb + ((int64_t)(cs + tok) * p.q_stride_n + (int64_t)(h * G + g) * 128) * 2;
     };
-    AFrag128 a;
-    a.load(qrow(R0), qrow(R1), j);
-    float acc[16][4];
-    qk_tile<BF16>(acc, a, s_k, r, j);
+    AFrag128 a_next;
+    if (warp < n_mt) a_next.load(qrow(warp * 16 + r), qrow(warp * 16 + r + 8), j);
+    for (int mt = warp; mt < n_mt; mt += kScThreads / 32) {
+      const int R0 = mt * 16 + r, R1 = R0 + 8;
+      const AFrag128 a = a_next;
+      const int mt2 = mt + kScThreads / 32;
+      if (mt2 < n_mt) a_next.load(qrow(mt2 * 16 + r), qrow(mt2 * 16 + r + 8), j);
+      float acc[16][4];
+      qk_tile<BF16>(acc, a, s_k, r, j);
 
-    // softmax over the chunk's keys, per row; lanes j=0..3 of a row share it
-    float m0 = -INFINITY, m1 = -INFINITY;
+      // softmax over the chunk's keys, per row; lanes j=0..3 of a row share it
+      float m0 = -INFINITY, m1 = -INFINITY;
 #pragma unroll
-    for (int nt = 0; nt < 16; ++nt) {
-      const int k0 = nt * 8 + 2 * j;
+      for (int nt = 0; nt < 16; ++nt) {
+        const int k0 = nt * 8 + 2 * j;
 #pragma unroll
-      for (int e = 0; e < 2; ++e) {
-        const bool ok = (k0 + e) < M;
-        acc[nt][e] = ok ? acc[nt][e] * p.scale_log2 : -INFINITY;
-        acc[nt][2 + e] = ok ? acc[nt][2 + e] * p.scale_log2 : -INFINITY;
-        m0 = fmaxf(m0, acc[nt][e]);
-        m1 = fmaxf(m1, acc[nt][2 + e]);
+        for (int e = 0; e < 2; ++e) {
+          const bool ok = (k0 + e) < M;
+          acc[nt][e] = ok ? acc[nt][e] * p.scale_log2 : -INFINITY;
+          acc[nt][2 + e] = ok ? acc[nt][2 + e] * p.scale_log2 : -INFINITY;
+          m0 = fmaxf(m0, acc[nt][e]);
+          m1 = fmaxf(m1, acc[nt][2 + e]);
+        }
+      }
+      m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 1));
+      m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 2));
+      m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 1));
+      m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 2));
+      float l0 = 0.f, l1 = 0.f;
+#pragma unroll
+      for (int nt = 0; nt < 16; ++nt) {
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          acc[nt][e] = ex2(acc[nt][e] - m0);
+          acc[nt][2 + e] = ex2(acc[nt][2 + e] - m1);
+          l0 += acc[nt][e];
+          l1 += acc[nt][2 + e];
+        }
+      }
+      l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
+      l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+      l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
+      l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+      const float i0 = (R0 < n_rows) ? 1.f / l0 : 0.f;
+      const float i1 = (R1 < n_rows) ? 1.f / l1 : 0.f;
+#pragma unroll
+      for (int nt = 0; nt < 16; ++nt) {
+        colacc[nt][0] += acc[nt][0] * i0 + acc[nt][2] * i1;
+        colacc[nt][1] += acc[nt][1] * i0 + acc[nt][3] * i1;
       }
     }
-    m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 1));
-    m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 2));
-    m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 1));
-    m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 2));
-    float l0 = 0.f, l1 = 0.f;
+    // column sums: over the 8 row-lanes of the warp, then over warps in fixed order
 #pragma unroll
     for (int nt = 0; nt < 16; ++nt) {
 #pragma unroll
       for (int e = 0; e < 2; ++e) {
-        acc[nt][e] = ex2(acc[nt][e] - m0);
-        acc[nt][2 + e] = ex2(acc[nt][2 + e] - m1);
-        l0 += acc[nt][e];
-        l1 += acc[nt][2 + e];
+        float v = colacc[nt][e];
+        v += __shfl_xor_sync(0xffffffffu, v, 4);
+        v += __shfl_xor_sync(0xffffffffu, v, 8);
+        v += __shfl_xor_sync(0xffffffffu, v, 16);
+        if (r == 0) s_col[warp][nt * 8 + 2 * j + e] = v;
       }
     }
-    l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
-    l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
-    l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
-    l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
-    const float i0 = (R0 < n_rows) ? 1.f / l0 : 0.f;
-    const float i1 = (R1 < n_rows) ? 1.f / l1 : 0.f;
+    __syncthreads();
+    // rows of the reference's last 64-row query tile that fall beyond the chunk add 1/chunk each
+    // (compactor.py:411-414,477-479)
+    const float pad = (float)(((M + kRefBlockM - 1) / kRefBlockM * kRefBlockM - M) * G) / (float)p.chunk;
+    float v = 0.f;
+    if (threadIdx.x < kKeyTile && (int)threadIdx.x < M) {
 #pragma unroll
-    for (int nt = 0; nt < 16; ++nt) {
-      colacc[nt][0] += acc[nt][0] * i0 + acc[nt][2] * i1;
-      colacc[nt][1] += acc[nt][1] * i0 + acc[nt][3] * i1;
+      for (int w = 0; w < kScThreads / 32; ++w) v += s_col[w][threadIdx.x];
+      v += pad;
+      p.raw[(int64_t)(cs + threadIdx.x) * p.HKV + h] = v;
     }
-  }
-  // column sums: over the 8 row-lanes of the warp, then over warps in fixed order
-#pragma unroll
-  for (int nt = 0; nt < 16; ++nt) {
-#pragma unroll
-    for (int e = 0; e < 2; ++e) {
-      float v = colacc[nt][e];
-      v += __shfl_xor_sync(0xffffffffu, v, 4);
-      v += __shfl_xor_sync(0xffffffffu, v, 8);
-      v += __shfl_xor_sync(0xffffffffu, v, 16);
-      if (r == 0) s_col[warp][nt * 8 + 2 * j + e] = v;
+    // per-item (sum, sumsq) for the per-sequence z-score
+    float s1 = ((int)threadIdx.x < M) ? v : 0.f, s2 = s1 * s1;
+    s1 = warp_sum(s1);
+    s2 = warp_sum(s2);
+    if (lane == 0) { s_red[0][warp] = s1; s_red[1][warp] = s2; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      float a1 = 0.f, a2 = 0.f;
+      for (int w = 0; w < kScThreads / 32; ++w) { a1 += s_red[0][w]; a2 += s_red[1][w]; }
+      float* dst = p.partials + (((int64_t)b * p.max_chunks + ci) * p.HKV + h) * 2;
+      dst[0] = a1;
+      dst[1] = a2;
     }
-  }
-  __syncthreads();
-  // rows of the reference's last 64-row query tile that fall beyond the chunk add 1/chunk each
-  // (compactor.py:411-414,477-479)
-  const float pad = (float)(((M + kRefBlockM - 1) / kRefBlockM * kRefBlockM - M) * G) / (float)p.chunk;
-  float v = 0.f;
-  if (threadIdx.x < kKeyTile && (int)threadIdx.x < M) {
-#pragma unroll
-    for (int w = 0; w < kScThreads / 32; ++w) v += s_col[w][threadIdx.x];
-    v += pad;
-    p.raw[(int64_t)(cs + threadIdx.x) * p.HKV + h] = v;
-  }
-  // per-CTA (sum, sumsq) for the per-sequence z-score
-  float s1 = (threadIdx.x < M) ? v : 0.f, s2 = s1 * s1;
-  s1 = warp_sum(s1);
-  s2 = warp_sum(s2);
-  __shared__ float s_red[2][kScThreads / 32];
-  if (lane == 0) { s_red[0][warp] = s1; s_red[1][warp] = s2; }
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    float a1 = 0.f, a2 = 0.f;
-    for (int w = 0; w < kScThreads / 32; ++w) { a1 += s_red[0][w]; a2 += s_red[1][w]; }
-    float* dst = p.partials + (((int64_t)b * p.max_chunks + ci) * p.HKV + h) * 2;
-    dst[0] = a1;
-    dst[1] = a2;
+    // the next iteration's prefetch overwrites buffer `buf` and its epilogue reuses s_col / s_red
+    __syncthreads();
+    cur = nxt;
+    buf ^= 1;
   }
 }
 
@@ -489,11 +545,22 @@ extern "C" int cvllm_chunk_attn_scores(const void* q, const void* k, int64_t q_s
   ChunkParams p;
   p.q = q; p.k = k; p.q_stride_n = q_stride_n; p.k_stride_n = k_stride_n; p.cu = cu_seqlens;
   p.raw = out; p.partials = reinterpret_cast<float*>(workspace);
-  p.HQ = HQ; p.HKV = HKV; p.G = HQ / HKV; p.chunk = chunk; p.max_chunks = max_chunks;
+  p.B = B; p.HQ = HQ; p.HKV = HKV; p.G = HQ / HKV; p.chunk = chunk; p.max_chunks = max_chunks;
+  p.n_ci = grid_chunks;
   p.scale_log2 = sm_scale * 1.4426950408889634f;
-  const dim3 grid(grid_chunks, HKV, B);
-  if (dtype == CVLLM_BF16) chunk_scores_kernel<true><<<grid, kScThreads, kScSmem, st>>>(p);
-  else chunk_scores_kernel<false><<<grid, kScThreads, kScSmem, st>>>(p);
+  const int64_t items = (int64_t)B * HKV * grid_chunks;
+  CVLLM_CHECK_SUPPORTED(items < (1ll << 31));
+  const int grid = (int)(items < sm_count() ? items : sm_count());
+  static bool attr_set = false;  // 2 K buffers = 80 KB dynamic smem (not a stream op: safe under capture)
+  if (!attr_set) {
+    CVLLM_CHECK_CUDA(cudaFuncSetAttribute(chunk_scores_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          2 * kScSmem));
+    CVLLM_CHECK_CUDA(cudaFuncSetAttribute(chunk_scores_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          2 * kScSmem));
+    attr_set = true;
+  }
+  if (dtype == CVLLM_BF16) chunk_scores_kernel<true><<<grid, kScThreads, 2 * kScSmem, st>>>(p);
+  else chunk_scores_kernel<false><<<grid, kScThreads, 2 * kScSmem, st>>>(p);
   CVLLM_CHECK_LAUNCH();
   ChunkFinalizeParams f;
   f.out = out; f.partials = p.partials; f.cu = cu_seqlens; f.accum = accum; f.accum_dtype = accum_dtype;

@@ -27,7 +27,8 @@ constexpr int kLevThreads = 256;
 constexpr int kSk = 48;            // sketch columns
 constexpr int kTokTile = 256;      // tokens per smem tile
 constexpr int kXtStride = kTokTile + 8;  // 16-bit elements per sketch row (pad: bank spread)
-constexpr int kJacobiSweeps = 10;
+constexpr int kJacobiSweeps = 8;     // upper bound (8 == 10 in score accuracy, tools/leverage_sweeps.py); sweeps stop once no rotation moves G any more
+constexpr int kEigThreads = 128;
 
 struct LevParams {
   const void* k;
@@ -35,6 +36,9 @@ struct LevParams {
   const int32_t* chunk_offsets;
   const void* phi;  // [128, 48] 16-bit
   float* raw;       // [N, HKV] fp32 (values already rounded to 16-bit)
+  float* gram;      // [n_chunks*HKV][48][48] fp32
+  float* mean;      // [n_chunks*HKV][48] fp32
+  float* sv;        // [n_chunks*HKV][48][48] fp32 (values rounded to 16-bit)
   int HKV;
   float reg;
 };
@@ -58,13 +62,10 @@ __device__ __forceinline__ float from16(uint16_t x) {
 struct LevSmem {
   uint16_t phiT[kSk][128 + 32];       // PHI^T: sketch-major, d contiguous (+64 B pad: conflict-free LDS.128)
   uint16_t xt[kSk][kXtStride];        // X^T tile: sketch-major, token contiguous
-  float g[kSk][kSk + 1];              // Gram -> diagonalised in place
-  float v[kSk][kSk + 1];              // eigenvectors (columns)
-  float sv[kSk][kSk];                 // round16(V |lam|^-1/2)
+  float g[kSk][kSk + 1];              // Gram accumulator (gram kernel) / unused (score kernel)
+  float sv[kSk][kSk];                 // round16(V |lam|^-1/2) (score kernel) / staging (gram kernel)
   float colsum[kSk];
   float mean[kSk];
-  float rot_c[kSk / 2], rot_s[kSk / 2];
-  int pair_p[kSk / 2], pair_q[kSk / 2];
 };
 
 // X^T tile for tokens [t0, t0+nt): xt[c][t] = round16(sum_d K[t][d] * PHI[d][c]) (optionally centred)
@@ -113,9 +114,18 @@ __device__ __forceinline__ void sketch_tile(LevSmem& sm, const LevParams& p, int
   }
 }
 
-// grid (n_chunks, HKV)
+__device__ __forceinline__ void load_phi(LevSmem& sm, const LevParams& p) {
+  const uint16_t* phi = reinterpret_cast<const uint16_t*>(p.phi);
+  for (int i = threadIdx.x; i < 128 * kSk; i += kLevThreads) {
+    const int d = i / kSk, c = i - d * kSk;
+    sm.phiT[c][d] = phi[i];
+  }
+}
+
+// ---- kernel 1: grid (n_chunks, HKV): column means + Gram of the centred sketch ----
+// out: gram[(ch*HKV+h)][48][48] = fp32(round16(Xc^T Xc)) + reg*I ; mean[(ch*HKV+h)][48]
 template <bool BF16>
-__global__ void __launch_bounds__(kLevThreads, 2) leverage_kernel(const LevParams p) {
+__global__ void __launch_bounds__(kLevThreads, 2) leverage_gram_kernel(const LevParams p) {
   extern __shared__ __align__(16) unsigned char lev_smem_raw[];
   LevSmem& sm = *reinterpret_cast<LevSmem*>(lev_smem_raw);
   const int ch = blockIdx.x, h = blockIdx.y;
@@ -123,16 +133,9 @@ __global__ void __launch_bounds__(kLevThreads, 2) leverage_kernel(const LevParam
   if (c_len <= 0) return;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
-  // PHI^T into smem; zero accumulators
-  {
-    const uint16_t* phi = reinterpret_cast<const uint16_t*>(p.phi);
-    for (int i = tid; i < 128 * kSk; i += kLevThreads) {
-      const int d = i / kSk, c = i - d * kSk;
-      sm.phiT[c][d] = phi[i];
-    }
-    if (tid < kSk) sm.colsum[tid] = 0.f;
-    for (int i = tid; i < kSk * (kSk + 1); i += kLevThreads) (&sm.g[0][0])[i] = 0.f;
-  }
+  load_phi(sm, p);
+  if (tid < kSk) sm.colsum[tid] = 0.f;
+  for (int i = tid; i < kSk * (kSk + 1); i += kLevThreads) (&sm.g[0][0])[i] = 0.f;
   __syncthreads();
 
   // ---- pass A: column means of X over the chunk ----
@@ -153,10 +156,17 @@ __global__ void __launch_bounds__(kLevThreads, 2) leverage_kernel(const LevParam
   __syncthreads();
 
   // ---- pass B: Gram of the centred sketch, G[i][j] = sum_t xc[t][i] xc[t][j] ----
-  // 6 x 6 tiles of 8 x 8; warp w owns (m-tile pair, n-tiles): use m16n8k16 with M = 16 sketch rows
   for (int t0 = 0; t0 < c_len; t0 += kTokTile) {
     const int nt = min(kTokTile, c_len - t0);
-    sketch_tile<BF16>(sm, p, h, c_beg + t0, nt, true);
+    // one tile and the uncentred sketch is still resident: centre it in place
+    if (c_len <= kTokTile) {
+      for (int i = tid; i < kSk * nt; i += kLevThreads) {
+        const int c = i / nt, t = i - c * nt;
+        sm.xt[c][t] = to16<BF16>(round16<BF16>(from16<BF16>(sm.xt[c][t]) - sm.mean[c]));
+      }
+    } else {
+      sketch_tile<BF16>(sm, p, h, c_beg + t0, nt, true);
+    }
     __syncthreads();
     // zero the padded token columns so partial k16 steps contribute nothing
     const int nt16 = (nt + 15) & ~15;
@@ -190,24 +200,52 @@ __global__ void __launch_bounds__(kLevThreads, 2) leverage_kernel(const LevParam
     }
     __syncthreads();
   }
-  // round the Gram to the 16-bit dtype (compactor.py:166,171,173), add the regulariser, V = I.
-  // Symmetrise from the upper triangle (staged through sv) so rounding cannot make G asymmetric.
+  // round the Gram to the 16-bit dtype (compactor.py:166,171,173), add the regulariser.
+  // Symmetrise from the upper triangle so rounding cannot make G asymmetric.
+  float* gout = p.gram + (int64_t)(ch * p.HKV + h) * kSk * kSk;
   for (int i = tid; i < kSk * kSk; i += kLevThreads) {
     const int a = i / kSk, b = i - a * kSk;
-    sm.sv[a][b] = round16<BF16>(a <= b ? sm.g[a][b] : sm.g[b][a]);
+    gout[i] = round16<BF16>(a <= b ? sm.g[a][b] : sm.g[b][a]) + ((a == b) ? p.reg : 0.f);
   }
-  __syncthreads();
-  for (int i = tid; i < kSk * kSk; i += kLevThreads) {
+  if (tid < kSk) p.mean[(int64_t)(ch * p.HKV + h) * kSk + tid] = sm.mean[tid];
+}
+
+// ---- kernel 2: grid (n_chunks * HKV): symmetric eigendecomposition, parallel cyclic Jacobi ----
+// 24 disjoint (p,q) pairs per round, 47 rounds per sweep (round-robin tournament).  A round is
+//   phase 1  24 threads: rotation (c,s) of each pair from the current G
+//   phase 2  all threads: G <- J^T G J as 24x24 independent 2x2 blocks, V <- V J
+// in place (every element belongs to exactly one block), two barriers per round.
+// out: sv[(ch*HKV+h)][48][48] = round16(V |lam|^-1/2)   (compactor.py:197: S of a symmetric G is |lam|)
+struct EigSmem {
+  float g[kSk][kSk + 1];
+  float v[kSk][kSk + 1];
+  float rot_c[kSk / 2], rot_s[kSk / 2];
+  int pair_p[kSk / 2], pair_q[kSk / 2];
+  int any_rot;
+};
+
+template <bool BF16>
+__global__ void __launch_bounds__(kEigThreads) leverage_eig_kernel(const float* __restrict__ gram,
+                                                                   float* __restrict__ sv_out,
+                                                                   const int32_t* __restrict__ chunk_offsets,
+                                                                   int HKV) {
+  __shared__ EigSmem sm;
+  const int ch = blockIdx.x / HKV;
+  if (chunk_offsets[ch + 1] - chunk_offsets[ch] <= 0) return;
+  const int tid = threadIdx.x;
+  const float* gin = gram + (int64_t)blockIdx.x * kSk * kSk;
+  for (int i = tid; i < kSk * kSk; i += kEigThreads) {
     const int a = i / kSk, b = i - a * kSk;
-    sm.g[a][b] = sm.sv[a][b] + ((a == b) ? p.reg : 0.f);
+    sm.g[a][b] = gin[i];
     sm.v[a][b] = (a == b) ? 1.f : 0.f;
   }
+  if (tid == 0) sm.any_rot = 0;
   __syncthreads();
 
-  // ---- parallel cyclic Jacobi: 24 disjoint (p,q) pairs per round, 47 rounds per sweep ----
+  constexpr int NP = kSk / 2;  // 24 pairs
   for (int sweep = 0; sweep < kJacobiSweeps; ++sweep) {
     for (int rnd = 0; rnd < kSk - 1; ++rnd) {
-      if (tid < kSk / 2) {
+      if (tid < NP) {
         // round-robin tournament: position 0 fixed, the others rotate
         const int n = kSk;
         int a = (tid == 0) ? 0 : 1 + (tid - 1 + rnd) % (n - 1);
@@ -221,43 +259,65 @@ __global__ void __launch_bounds__(kLevThreads, 2) leverage_kernel(const LevParam
           const float t = (tau >= 0.f ? 1.f : -1.f) / (fabsf(tau) + sqrtf(1.f + tau * tau));
           c = rsqrtf(1.f + t * t);
           s = t * c;
+          // still moving? (below this the rotation is the identity in fp32)
+          if (fabsf(apq) > 1e-7f * sqrtf(fabsf(app * aqq))) sm.any_rot = 1;
         }
         sm.rot_c[tid] = c; sm.rot_s[tid] = s; sm.pair_p[tid] = pp; sm.pair_q[tid] = qq;
       }
       __syncthreads();
-      // rows: G <- J^T G
-      for (int i = tid; i < (kSk / 2) * kSk; i += kLevThreads) {
-        const int pr = i / kSk, col = i - pr * kSk;
-        const int pp = sm.pair_p[pr], qq = sm.pair_q[pr];
-        const float c = sm.rot_c[pr], s = sm.rot_s[pr];
-        const float gp = sm.g[pp][col], gq = sm.g[qq][col];
-        sm.g[pp][col] = c * gp - s * gq;
-        sm.g[qq][col] = s * gp + c * gq;
+      // G blocks (i, j): rows {p_i, q_i} x cols {p_j, q_j}
+      for (int it = tid; it < NP * NP; it += kEigThreads) {
+        const int i = it / NP, j = it - i * NP;
+        const int pi = sm.pair_p[i], qi = sm.pair_q[i], pj = sm.pair_p[j], qj = sm.pair_q[j];
+        const float ci = sm.rot_c[i], si = sm.rot_s[i], cj = sm.rot_c[j], sj = sm.rot_s[j];
+        const float gpp = sm.g[pi][pj], gpq = sm.g[pi][qj], gqp = sm.g[qi][pj], gqq = sm.g[qi][qj];
+        const float rpp = ci * gpp - si * gqp, rpq = ci * gpq - si * gqq;  // J_i^T . (rows)
+        const float rqp = si * gpp + ci * gqp, rqq = si * gpq + ci * gqq;
+        sm.g[pi][pj] = cj * rpp - sj * rpq;                                // . J_j (columns)
+        sm.g[pi][qj] = sj * rpp + cj * rpq;
+        sm.g[qi][pj] = cj * rqp - sj * rqq;
+        sm.g[qi][qj] = sj * rqp + cj * rqq;
       }
-      __syncthreads();
-      // columns: G <- G J, V <- V J
-      for (int i = tid; i < (kSk / 2) * kSk; i += kLevThreads) {
-        const int pr = i / kSk, row = i - pr * kSk;
-        const int pp = sm.pair_p[pr], qq = sm.pair_q[pr];
-        const float c = sm.rot_c[pr], s = sm.rot_s[pr];
-        const float gp = sm.g[row][pp], gq = sm.g[row][qq];
-        sm.g[row][pp] = c * gp - s * gq;
-        sm.g[row][qq] = s * gp + c * gq;
-        const float vp = sm.v[row][pp], vq = sm.v[row][qq];
-        sm.v[row][pp] = c * vp - s * vq;
-        sm.v[row][qq] = s * vp + c * vq;
+      // V <- V J
+      for (int it = tid; it < NP * kSk; it += kEigThreads) {
+        const int i = it / kSk, row = it - i * kSk;
+        const int pi = sm.pair_p[i], qi = sm.pair_q[i];
+        const float c = sm.rot_c[i], s = sm.rot_s[i];
+        const float vp = sm.v[row][pi], vq = sm.v[row][qi];
+        sm.v[row][pi] = c * vp - s * vq;
+        sm.v[row][qi] = s * vp + c * vq;
       }
       __syncthreads();
     }
+    const bool done = sm.any_rot == 0;
+    __syncthreads();
+    if (done) break;
+    if (tid == 0) sm.any_rot = 0;
+    __syncwarp();
   }
-  // SV = round16(V |lam|^-1/2)   (compactor.py:197: singular values of a symmetric G are |lam|)
-  for (int i = tid; i < kSk * kSk; i += kLevThreads) {
+  float* out = sv_out + (int64_t)blockIdx.x * kSk * kSk;
+  for (int i = tid; i < kSk * kSk; i += kEigThreads) {
     const int a = i / kSk, b = i - a * kSk;
-    sm.sv[a][b] = round16<BF16>(sm.v[a][b] * rsqrtf(fabsf(sm.g[b][b])));
+    out[i] = round16<BF16>(sm.v[a][b] * rsqrtf(fabsf(sm.g[b][b])));
+  }
+}
+
+// ---- kernel 3: grid (n_chunks, HKV): score_t = round16(sum_j round16(round16(xc_t . sv_j)^2)) ----
+template <bool BF16>
+__global__ void __launch_bounds__(kLevThreads, 2) leverage_score_kernel(const LevParams p) {
+  extern __shared__ __align__(16) unsigned char lev_smem_raw[];
+  LevSmem& sm = *reinterpret_cast<LevSmem*>(lev_smem_raw);
+  const int ch = blockIdx.x, h = blockIdx.y;
+  const int c_beg = p.chunk_offsets[ch], c_len = p.chunk_offsets[ch + 1] - c_beg;
+  if (c_len <= 0) return;
+  const int tid = threadIdx.x;
+  load_phi(sm, p);
+  {
+    const float* svin = p.sv + (int64_t)(ch * p.HKV + h) * kSk * kSk;
+    for (int i = tid; i < kSk * kSk; i += kLevThreads) (&sm.sv[0][0])[i] = svin[i];
+    if (tid < kSk) sm.mean[tid] = p.mean[(int64_t)(ch * p.HKV + h) * kSk + tid];
   }
   __syncthreads();
-
-  // ---- pass C: score_t = round16(sum_j round16(round16(xc_t . sv_j)^2)) ----
   for (int t0 = 0; t0 < c_len; t0 += kTokTile) {
     const int nt = min(kTokTile, c_len - t0);
     sketch_tile<BF16>(sm, p, h, c_beg + t0, nt, true);
@@ -335,10 +395,14 @@ __global__ void __launch_bounds__(256) leverage_finalize_kernel(const float* __r
 
 using namespace cvllm;
 
+static size_t lev_align(size_t x) { return (x + 255) & ~(size_t)255; }
+
 extern "C" size_t cvllm_leverage_scores_workspace_bytes(int N, int HKV, int sketch, int n_chunks) {
-  (void)sketch; (void)n_chunks;
+  (void)sketch;
   if (N <= 0 || HKV <= 0) return 256;
-  return (((size_t)N * HKV * sizeof(float)) + 255) & ~(size_t)255;
+  const size_t mats = (size_t)(n_chunks > 0 ? n_chunks : 0) * HKV;
+  return lev_align((size_t)N * HKV * sizeof(float)) + 2 * lev_align(mats * kSk * kSk * sizeof(float)) +
+         lev_align(mats * kSk * sizeof(float));
 }
 
 extern "C" int cvllm_leverage_scores(const void* k_pre, int64_t k_stride_n, int64_t k_stride_h,
@@ -354,26 +418,39 @@ extern "C" int cvllm_leverage_scores(const void* k_pre, int64_t k_stride_n, int6
   CVLLM_CHECK_ALIGN(aligned16(k_pre) && k_stride_n % 8 == 0 && k_stride_h % 8 == 0);
   CVLLM_CHECK_ARG(workspace_bytes >= cvllm_leverage_scores_workspace_bytes(N, HKV, sketch, n_chunks));
   auto st = static_cast<cudaStream_t>(stream);
+  const size_t mats = (size_t)n_chunks * HKV;
+  char* wsb = reinterpret_cast<char*>(workspace);
   LevParams p;
   p.k = k_pre; p.k_stride_n = k_stride_n; p.k_stride_h = k_stride_h; p.chunk_offsets = chunk_offsets;
-  p.phi = phi; p.raw = reinterpret_cast<float*>(workspace); p.HKV = HKV; p.reg = regularizer;
+  p.phi = phi; p.HKV = HKV; p.reg = regularizer;
+  p.raw = reinterpret_cast<float*>(wsb);
+  wsb += lev_align((size_t)N * HKV * sizeof(float));
+  p.gram = reinterpret_cast<float*>(wsb);
+  wsb += lev_align(mats * kSk * kSk * sizeof(float));
+  p.sv = reinterpret_cast<float*>(wsb);
+  wsb += lev_align(mats * kSk * kSk * sizeof(float));
+  p.mean = reinterpret_cast<float*>(wsb);
   const size_t smem = sizeof(LevSmem);
   static bool attr_set = false;
   if (!attr_set) {
-    CVLLM_CHECK_CUDA(cudaFuncSetAttribute(leverage_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          (int)smem));
-    CVLLM_CHECK_CUDA(cudaFuncSetAttribute(leverage_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          (int)smem));
+    CVLLM_CHECK_CUDA(cudaFuncSetAttribute(leverage_gram_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CVLLM_CHECK_CUDA(cudaFuncSetAttribute(leverage_gram_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CVLLM_CHECK_CUDA(cudaFuncSetAttribute(leverage_score_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CVLLM_CHECK_CUDA(cudaFuncSetAttribute(leverage_score_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_set = true;
   }
   const dim3 grid(n_chunks, HKV);
   if (dtype == CVLLM_BF16) {
-    leverage_kernel<true><<<grid, kLevThreads, smem, st>>>(p);
+    leverage_gram_kernel<true><<<grid, kLevThreads, smem, st>>>(p);
+    leverage_eig_kernel<true><<<(unsigned)mats, kEigThreads, 0, st>>>(p.gram, p.sv, chunk_offsets, HKV);
+    leverage_score_kernel<true><<<grid, kLevThreads, smem, st>>>(p);
     leverage_finalize_kernel<true><<<n_chunks, 256, 0, st>>>(p.raw, chunk_offsets, out_scores, HKV, normalize);
   } else {
-    leverage_kernel<false><<<grid, kLevThreads, smem, st>>>(p);
+    leverage_gram_kernel<false><<<grid, kLevThreads, smem, st>>>(p);
+    leverage_eig_kernel<false><<<(unsigned)mats, kEigThreads, 0, st>>>(p.gram, p.sv, chunk_offsets, HKV);
+    leverage_score_kernel<false><<<grid, kLevThreads, smem, st>>>(p);
     leverage_finalize_kernel<false><<<n_chunks, 256, 0, st>>>(p.raw, chunk_offsets, out_scores, HKV, normalize);
   }
-  CVLLM_CHECK_LAUNCHES(2);
+  CVLLM_CHECK_LAUNCHES(4);
   return CVLLM_OK;
 }

@@ -10,14 +10,10 @@
 // scores; ordering rule everywhere: key descending, ties by ascending flat
 // index (tok*H + head), NaN above +inf.  Rows land in ascending token order.
 #include "common.cuh"
+#include "select_common.cuh"
 
 namespace cvllm {
 
-constexpr int kSelThreads = 1024;
-
-__device__ __forceinline__ uint32_t load_key(const float* scores, int64_t stride_n, int n, int h) {
-  return score_key(__float_as_uint(__ldg(scores + (int64_t)n * stride_n + h)));
-}
 
 // ===========================================================================
 // A. full ranking: stable LSD radix sort, 4 x 8-bit passes, multi-block
@@ -199,88 +195,9 @@ __device__ SelectResult block_radix_select(F f, int cnt, uint32_t k, uint32_t* s
   return r;
 }
 
-// CTA-wide exclusive prefix of a 0/1 flag in thread order; returns the prefix,
-// total via s_total.  kSelThreads threads.
-__device__ __forceinline__ int block_excl_count(bool flag, int* s_warp /*[32]*/, int& total) {
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const uint32_t m = __ballot_sync(0xffffffffu, flag);
-  if (lane == 0) s_warp[warp] = __popc(m);
-  __syncthreads();
-  int before = 0, tot = 0;
-  const int nw = blockDim.x >> 5;
-  for (int w = 0; w < nw; ++w) {
-    const int c = s_warp[w];
-    if (w < warp) before += c;
-    tot += c;
-  }
-  __syncthreads();
-  total = tot;
-  return before + __popc(m & ((1u << lane) - 1u));
-}
-
-// pad rule of store_kv_cache.py:205-248 in closed form
-__device__ __forceinline__ int pad_amount(int L_after_topk, int ctx_len, int PS) {
-  const int mod = L_after_topk % PS;
-  if (mod == 0) return 0;
-  const int need = PS - mod;
-  const int max_add = ctx_len - L_after_topk;
-  return max(0, min(need, max_add));
-}
-
 // ===========================================================================
-// C. fused path: global select -> per-head select + ordered compaction
+// C. ordered compaction from keep flags (index flavour) + row gather
 // ===========================================================================
-// one CTA per sequence: threshold over all len*H entries, then per-head counts
-// of the selected set and the per-head target n_h (after padding).
-__global__ void __launch_bounds__(kSelThreads) select_global_kernel(
-    const float* __restrict__ scores, int64_t stride_n, const int32_t* __restrict__ cu,
-    const int32_t* __restrict__ num_retain, const int32_t* __restrict__ batch_mapping,
-    const int32_t* __restrict__ bh_lens, int H, int PS, int pad_to_page, int reserved_batch,
-    int32_t* __restrict__ n_keep /*[B,H]*/) {
-  __shared__ uint32_t s_hist[256];
-  __shared__ uint32_t s_bcast[2];
-  __shared__ int s_warp[32];
-  __shared__ int s_cnt[64];
-  const int b = blockIdx.x;
-  const int beg = cu[b], len = cu[b + 1] - beg;
-  const int cnt = len * H;
-  if (threadIdx.x < H) s_cnt[threadIdx.x] = 0;
-  __syncthreads();
-  uint32_t k = (uint32_t)max(0, min(num_retain[b], cnt));
-  const bool skip = (batch_mapping[b] == reserved_batch) || k == 0 || cnt == 0;
-  if (skip) {
-    if (threadIdx.x < H) n_keep[b * H + threadIdx.x] = 0;
-    return;
-  }
-  auto f = [&](int i) {
-    const int tok = i / H, h = i - tok * H;
-    return load_key(scores, stride_n, beg + tok, h);
-  };
-  const SelectResult sr = block_radix_select(f, cnt, k, s_hist, s_bcast);
-  // ordered pass: ties taken in ascending flat index
-  int ties_seen = 0;
-  for (int base = 0; base < cnt; base += kSelThreads) {
-    const int i = base + threadIdx.x;
-    uint32_t key = 0;
-    const bool valid = i < cnt;
-    if (valid) key = f(i);
-    const bool tie = valid && key == sr.thresh;
-    int tot;
-    const int trank = ties_seen + block_excl_count(tie, s_warp, tot);
-    ties_seen += tot;
-    const bool sel = valid && (key > sr.thresh || (tie && trank < (int)sr.ties));
-    if (sel) atomicAdd(&s_cnt[i % H], 1);
-  }
-  __syncthreads();
-  if (threadIdx.x < H) {
-    const int h = threadIdx.x;
-    const int c = s_cnt[h];
-    int n = c;
-    if (pad_to_page) n += pad_amount(bh_lens[b * H + h] + c, len, PS);
-    n_keep[b * H + h] = min(n, len);
-  }
-}
-
 // one CTA per (head, sequence): PRED == 0: threshold the head's own scores at
 // n_keep[b,h]; PRED == 1: use the keep flags.  Ordered pass writes the
 // destination logical position of every kept (token, head) into pos[n*H+h]
@@ -536,7 +453,7 @@ static int gather_dispatch(int vpr, const void* keys, const void* vals, int64_t 
   return CVLLM_OK;
 }
 
-static int check_store_args(const void* keys, const void* vals, int64_t sk_n, int64_t sk_h, int64_t sv_n,
+int cvllm_check_store_args(const void* keys, const void* vals, int64_t sk_n, int64_t sk_h, int64_t sv_n,
                             int64_t sv_h, void* k_cache, void* v_cache, int D, int elem_bytes, int H,
                             int* vpr_out, int64_t* per16_out) {
   CVLLM_CHECK_ARG(elem_bytes == 1 || elem_bytes == 2 || elem_bytes == 4);
@@ -573,7 +490,7 @@ extern "C" int cvllm_prefill_store_topk_idx(
   if (N == 0) return CVLLM_OK;
   int vpr;
   int64_t per16;
-  const int rc = check_store_args(keys, vals, sk_n, sk_h, sv_n, sv_h, k_cache, v_cache, D, elem_bytes,
+  const int rc = cvllm_check_store_args(keys, vals, sk_n, sk_h, sv_n, sv_h, k_cache, v_cache, D, elem_bytes,
                                   HKV, &vpr, &per16);
   if (rc != CVLLM_OK) return rc;
   CVLLM_CHECK_ARG(workspace_bytes >= cvllm_store_topk_workspace_bytes(B, HKV, N, max_sel));
@@ -617,45 +534,3 @@ extern "C" int cvllm_prefill_store_topk_idx(
   return CVLLM_OK;
 }
 
-extern "C" size_t cvllm_select_store_workspace_bytes(int B, int H, int N) {
-  if (B <= 0 || H <= 0 || N < 0) return 0;
-  return align256((size_t)N * H * 4) + align256((size_t)B * H * 4);
-}
-
-extern "C" int cvllm_select_store_topk(const float* scores, int64_t s_stride_n, const void* keys,
-                                       const void* vals, int64_t sk_n, int64_t sk_h, int64_t sv_n,
-                                       int64_t sv_h, const int32_t* num_retain,
-                                       const int32_t* cu_seqlens_k, const int32_t* batch_mapping,
-                                       int32_t* bh_lens, const int32_t* page_table, void* k_cache,
-                                       void* v_cache, int B, int N, int HKV, int D, int PS, int NLP,
-                                       int elem_bytes, int pad_to_page, int reserved_batch,
-                                       void* workspace, size_t workspace_bytes, cvllm_stream_t stream) {
-  CVLLM_CHECK_ARG(B > 0 && N >= 0 && HKV > 0 && D > 0 && PS > 0 && NLP > 0);
-  CVLLM_CHECK_ARG(scores && keys && vals && num_retain && cu_seqlens_k && batch_mapping && bh_lens &&
-                  page_table && k_cache && v_cache && workspace);
-  if (N == 0) return CVLLM_OK;
-  int vpr;
-  int64_t per16;
-  const int rc = check_store_args(keys, vals, sk_n, sk_h, sv_n, sv_h, k_cache, v_cache, D, elem_bytes,
-                                  HKV, &vpr, &per16);
-  if (rc != CVLLM_OK) return rc;
-  CVLLM_CHECK_ARG(workspace_bytes >= cvllm_select_store_workspace_bytes(B, HKV, N));
-  char* w = reinterpret_cast<char*>(workspace);
-  int32_t* pos = reinterpret_cast<int32_t*>(w);
-  int32_t* n_keep = reinterpret_cast<int32_t*>(w + align256((size_t)N * HKV * 4));
-  auto st = static_cast<cudaStream_t>(stream);
-  select_global_kernel<<<B, kSelThreads, 0, st>>>(scores, s_stride_n, cu_seqlens_k, num_retain,
-                                                  batch_mapping, bh_lens, HKV, PS, pad_to_page,
-                                                  reserved_batch, n_keep);
-  CVLLM_CHECK_LAUNCH();
-  compact_head_kernel<0><<<dim3(HKV, B), kSelThreads, 0, st>>>(scores, s_stride_n, nullptr, cu_seqlens_k,
-                                                               batch_mapping, n_keep, bh_lens, HKV,
-                                                               reserved_batch, pos);
-  CVLLM_CHECK_LAUNCH();
-  const int g = gather_dispatch(vpr, keys, vals, sk_n / per16, sk_h / per16, sv_n / per16, sv_h / per16,
-                                pos, cu_seqlens_k, batch_mapping, page_table, k_cache, v_cache, B, N,
-                                HKV, PS, NLP, st);
-  if (g != CVLLM_OK) return g;
-  CVLLM_CHECK_LAUNCH();
-  return CVLLM_OK;
-}

@@ -42,7 +42,7 @@ def zscore_segments_(scores: torch.Tensor, seg_offsets: Sequence[int]) -> None:
 
 def approximate_leverage_scores(key_states: torch.Tensor, context_lens: List[int], PHI: torch.Tensor,
                                 regularizer: float = 5e-3, normalize: bool = False, chunk_size: int = 512,
-                                emulate_dtype: bool = True) -> torch.Tensor:
+                                emulate_dtype: bool = True, factorization: str = "svd32") -> torch.Tensor:
     """compression/compactor.py:113-221.
 
     X = K_h PHI; per chunk: centre, G = X^T X + reg*I, (V,S) = svd(G),
@@ -50,6 +50,12 @@ def approximate_leverage_scores(key_states: torch.Tensor, context_lens: List[int
     emulate_dtype=True keeps the reference's rounding points (X, the centred chunk, the Gram,
     V S^-1/2, U and the row sums all live in K's dtype, :158,165-171,197,209-210);
     emulate_dtype=False evaluates the same formula in fp32 from the same inputs.
+    factorization: "svd32" = torch.linalg.svd in fp32, the reference's arithmetic (:177 uses cuSOLVER
+    gesvda, an approximate fp32 SVD); "eigh64" = exact symmetric eigendecomposition in fp64 of the SAME
+    (rounded) Gram, singular values |lambda| — the noise-free answer both fp32 factorisations
+    approximate.  On low-rank keys the 16-bit Gram is indefinite with |lambda| down to ~1e-2 against
+    lambda_max ~1e5, so scores move by O(1) between fp32 factorisations; tests measure distances to
+    "eigh64" and require ours to be no larger than "svd32"'s.
     Returns [N, H] in K's dtype.
     """
     dt = key_states.dtype if emulate_dtype else torch.float32
@@ -69,7 +75,11 @@ def approximate_leverage_scores(key_states: torch.Tensor, context_lens: List[int
         chunk = chunk - chunk.mean(dim=-2, keepdim=True)
         g = torch.matmul(chunk.transpose(-1, -2), chunk).to(torch.float32)  # [H, k, k]
         g = g + regularizer * torch.eye(k)
-        V, S, _ = torch.linalg.svd(g, full_matrices=False)
+        if factorization == "eigh64":
+            lam, V = torch.linalg.eigh(g.double())
+            S, V = lam.abs().float(), V.float()
+        else:
+            V, S, _ = torch.linalg.svd(g, full_matrices=False)
         SV = (V * S.rsqrt().unsqueeze(-2)).to(dt)
         U = torch.matmul(chunk, SV)
         out[s:e] = (U * U).sum(dim=-1).clamp_min(0.0).transpose(0, 1)
