@@ -483,6 +483,26 @@ def main():
         ms_comp = max_over_ranks(time_loop(w.compress_only, max(3, args.steps // 2)))
         comps["compress_mtok_s"] = n_tok * world / (ms_comp * 1e-3) / 1e6
         comps["compress_ms"] = ms_comp
+        # the same chain replayed from a CUDA graph: device time without the Python launch path
+        try:
+            gstream = torch.cuda.Stream(device=dev)
+            gstream.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(gstream):
+                w.compress_only()  # workspaces for this stream
+                torch.cuda.synchronize()
+                graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(graph, stream=gstream):
+                    w.compress_only()
+            torch.cuda.synchronize()
+            for _ in range(2):
+                graph.replay()
+            torch.cuda.synchronize()
+            ms_graph = max_over_ranks(time_loop(graph.replay, max(3, args.steps // 2)))
+            comps["compress_graph_ms"] = ms_graph
+            comps["compress_graph_mtok_s"] = n_tok * world / (ms_graph * 1e-3) / 1e6
+            del graph
+        except Exception as ex:  # capture is a measurement aid, not part of the path
+            comps["compress_graph_error"] = repr(ex)[:200]
         comp_bytes = n_tok * (2048 + 8192 + 2048 + HKV * 4 * 4) + kept_pairs * 1024
         comps["compress_implied_gbs"] = comp_bytes / (ms_comp * 1e-3) / 1e9
 

@@ -62,6 +62,36 @@ def split_into_chunks(xs, chunk_size):
     return coalesced, chunks
 
 
+_OFFSETS_CACHE: dict = {}
+
+
+def _chunk_offsets(chunk_lens: tuple, dev: torch.device) -> torch.Tensor:
+    """Device int32 prefix offsets of the chunks; cached per shape so a steady-state step issues no
+    host->device copy (and the whole scoring chain can be captured in a CUDA graph)."""
+    key = (chunk_lens, dev.index)
+    t = _OFFSETS_CACHE.get(key)
+    if t is None:
+        offs = [0]
+        for c in chunk_lens:
+            offs.append(offs[-1] + c)
+        t = torch.tensor(offs, dtype=torch.int32, device=dev)
+        if len(_OFFSETS_CACHE) > 64:
+            _OFFSETS_CACHE.clear()
+        _OFFSETS_CACHE[key] = t
+    return t
+
+
+def _protected_counts(pf: tuple, pl: tuple, dev: torch.device) -> torch.Tensor:
+    key = ("prot", pf, pl, dev.index)
+    t = _OFFSETS_CACHE.get(key)
+    if t is None:
+        t = torch.tensor(list(pf) + list(pl), dtype=torch.int32, device=dev)
+        if len(_OFFSETS_CACHE) > 64:
+            _OFFSETS_CACHE.clear()
+        _OFFSETS_CACHE[key] = t
+    return t
+
+
 def approximate_leverage_scores(
     key_states: torch.Tensor,  # [N, H, D]
     context_lens: List[int],  # [B]
@@ -87,10 +117,7 @@ def approximate_leverage_scores(
         chunk_lens = list(context_lens)
     assert sum(chunk_lens) == Ntok
     dev = key_states.device
-    offs = [0]
-    for c in chunk_lens:
-        offs.append(offs[-1] + c)
-    offsets = torch.tensor(offs, dtype=torch.int32).pin_memory().to(dev, non_blocking=True)
+    offsets = _chunk_offsets(tuple(chunk_lens), dev)
     out = torch.empty((Ntok, H), dtype=key_states.dtype, device=dev)
     if Ntok == 0:
         return out
@@ -151,7 +178,7 @@ def non_causal_attn_scores(
     if protected_first_tokens is not None or protected_last_tokens is not None:
         pf_l = list(protected_first_tokens) if protected_first_tokens is not None else [0] * B
         pl_l = list(protected_last_tokens) if protected_last_tokens is not None else [0] * B
-        both = torch.tensor(pf_l + pl_l, dtype=torch.int32).pin_memory().to(dev, non_blocking=True)
+        both = _protected_counts(tuple(pf_l), tuple(pl_l), dev)
         pf, pl = both[:B], both[B:]
     blend = 1.0 if accum_blending is None else float(accum_blending)
     acc_dtype, acc_stride = 2, 0

@@ -430,6 +430,13 @@ umma_selftest_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_cons
 
 using namespace cvllm;
 
+int cvllm_launch_prefill2(const CUtensorMap& tm_q, const CUtensorMap& tm_k, const CUtensorMap& tm_v,
+                          const CUtensorMap& tm_kc, const CUtensorMap& tm_vc, void* out,
+                          const int32_t* seq_lens_bh, const int32_t* page_table,
+                          const int32_t* batch_mapping, const int32_t* cu_seqlens_q, int B, int HQ,
+                          int HKV, int PS, int NLP, int64_t o_stride_n, int max_seqlen_q,
+                          float scale_log2, float rescale_threshold, bool bf16, cudaStream_t st);
+
 extern "C" int cvllm_prefill_attention(const void* q, const void* k, const void* v, void* out,
                                        const void* k_cache, const void* v_cache,
                                        const int32_t* seq_lens_bh, const int32_t* page_table,
@@ -485,9 +492,15 @@ extern "C" int cvllm_prefill_attention(const void* q, const void* k, const void*
   // test hook: 0 forces an O rescale whenever a row max grows (exercises the correction path)
   if (const char* e = getenv("CVLLM_PREFILL_THRESHOLD")) p.rescale_threshold = (float)atof(e);
 
+  auto st = static_cast<cudaStream_t>(stream);
+  // even GQA group: two query heads of one KV head per CTA, ping-ponged S accumulators
+  // (prefill_attn2.cu).  CVLLM_PREFILL_V1=1 forces the one-head-per-CTA kernel (tests cover both).
+  if ((HQ / HKV) % 2 == 0 && !getenv("CVLLM_PREFILL_V1"))
+    return cvllm_launch_prefill2(tm_q, tm_k, tm_v, tm_kc, tm_vc, out, seq_lens_bh, page_table,
+                                 batch_mapping, cu_seqlens_q, B, HQ, HKV, PS, NLP, o_stride_n,
+                                 max_seqlen_q, p.scale_log2, p.rescale_threshold, bf16, st);
   const size_t smem = sizeof(PrefillSmem) + 1024;
   const dim3 grid((max_seqlen_q + kBM - 1) / kBM, HQ, B);
-  auto st = static_cast<cudaStream_t>(stream);
   if (bf16) {
     CVLLM_CHECK_CUDA(cudaFuncSetAttribute(prefill_attn_kernel<true>,
                                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -1,0 +1,417 @@
+// Causal head-sparse varlen prefill attention, two query tiles per CTA (GQA pairs).
+//
+// Same contract as prefill_attn.cu (attention/sparse_varlen_kernel.py:11-197,265-519), used when
+// the GQA group size is even.  One CTA = 128 query tokens x TWO query heads of the same KV head:
+// the K / V tiles are loaded once and feed both heads, and — the point — the two S = Q.K^T
+// accumulators ping-pong so the tensor pipe never waits for a softmax:
+//
+//   tensor pipe :  S0(0) S1(0) | PV0(0) S0(1) PV1(0) S1(1) | PV0(1) S0(2) PV1(1) S1(2) | ...
+//   softmax WG0 :        [ S0(0) -> P0(0) ]          [ S0(1) -> P0(1) ]
+//   softmax WG1 :              [ S1(0) -> P1(0) ]          [ S1(1) -> P1(1) ]
+//
+// i.e. each softmax warpgroup has two UMMA tiles (PV of the other head + the other head's next
+// QK^T) of time to turn S into P before its own PV is due.
+//
+//   warps 0-3     softmax of head 0: one thread per query row, S row TMEM -> registers, running
+//   warps 4-7     softmax of head 1  max with lazy O rescale (only when the max grows by > 8 in
+//                 log2 units), P written back over S as packed 16-bit, epilogue O / l.
+//   warp 8        TMA producer: Q0, Q1 once; K_j, V_j through ONE ring of 5 x 32 KB slots
+//                 (K0 V0 K1 V1 ...).  Prefix tiles straight from the paged cache (a 128-row tile
+//                 never crosses a page), new-token tiles from the packed k / v.
+//   warp 9        UMMA issuer (single thread): QK^T as SS, PV as TS (P read from TMEM).
+//   warps 10-11   idle (registers are handed out per 4-warp group: the third group gives its
+//                 registers to the softmax groups with setmaxnreg, 56 vs 224 per thread).
+//
+// TMEM (512 columns): S0 [0,128)  S1 [128,256)  O0 [256,384)  O1 [384,512).
+#include <stdlib.h>
+
+#include "common.cuh"
+#include "tma.cuh"
+
+namespace cvllm {
+
+namespace p2 {
+constexpr int kBM = 128, kBN = 128, kHD = 128;
+constexpr int kSlots = 5;
+constexpr int kTileBytes = kBN * kHD * 2;  // 32 KB
+constexpr int kBoxBytes = kTileBytes / 2;  // one [128 x 64] swizzled box
+constexpr int kThreads = 384;              // 3 warpgroups
+constexpr int kRegsSoftmax = 224, kRegsOther = 56;  // 2*128*224 + 128*56 = 64512 <= 65536
+}  // namespace p2
+
+struct Prefill2Params {
+  void* out;
+  const int32_t* seq_lens_bh;
+  const int32_t* page_table;
+  const int32_t* batch_mapping;
+  const int32_t* cu_seqlens_q;
+  int B, HQ, HKV, G, PS, NLP;
+  int64_t o_stride_n;
+  float scale_log2;
+  float rescale_threshold;
+};
+
+struct Prefill2Smem {
+  unsigned char q[2][p2::kTileBytes];
+  unsigned char kv[p2::kSlots][p2::kTileBytes];
+  uint64_t q_full;
+  uint64_t full[p2::kSlots], empty[p2::kSlots];
+  uint64_t s_full[2], p_full[2];
+  uint64_t o_done[2];   // one phase per PV_t(i)
+  uint64_t o_final[2];  // last PV_t complete
+  uint32_t tmem_base;
+};
+
+template <bool BF16>
+__global__ void __launch_bounds__(p2::kThreads, 1)
+prefill_attn2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
+                     const __grid_constant__ CUtensorMap tm_v, const __grid_constant__ CUtensorMap tm_kc,
+                     const __grid_constant__ CUtensorMap tm_vc, const Prefill2Params p) {
+  using namespace p2;
+  extern __shared__ unsigned char smem_raw[];
+  Prefill2Smem& sm = *reinterpret_cast<Prefill2Smem*>(
+      (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int b = blockIdx.z;
+  const int hq0 = 2 * blockIdx.y;  // heads hq0, hq0 + 1 share KV head hkv (G even)
+  const int hkv = hq0 / p.G;
+  const int q_beg = p.cu_seqlens_q[b];
+  const int La = p.cu_seqlens_q[b + 1] - q_beg;
+  const int n_qt = (La + kBM - 1) / kBM;
+  const int qt = n_qt - 1 - (int)blockIdx.x;  // heaviest (latest) tiles first
+  if (qt < 0) return;
+  const int q0 = qt * kBM;
+  const int Lc = p.seq_lens_bh[b * p.HKV + hkv];
+  const int n_pre = (Lc + kBN - 1) / kBN;
+  const int n_tiles = n_pre + qt + 1;
+
+  // ---------------- setup ----------------
+  if (threadIdx.x == 0) {
+    mbar_init(&sm.q_full, 1);
+    for (int s = 0; s < kSlots; ++s) {
+      mbar_init(&sm.full[s], 1);
+      mbar_init(&sm.empty[s], 1);
+    }
+    for (int t = 0; t < 2; ++t) {
+      mbar_init(&sm.s_full[t], 1);
+      mbar_init(&sm.p_full[t], 128);
+      mbar_init(&sm.o_done[t], 1);
+      mbar_init(&sm.o_final[t], 1);
+    }
+    mbar_fence_init();
+  }
+  if (warp == 9) {
+    tmem_alloc(&sm.tmem_base, 512);
+    tmem_relinquish();
+  }
+  if (warp == 8 && lane == 0) {
+    tma_prefetch_desc(&tm_q);
+    tma_prefetch_desc(&tm_k);
+    tma_prefetch_desc(&tm_v);
+    tma_prefetch_desc(&tm_kc);
+    tma_prefetch_desc(&tm_vc);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = sm.tmem_base;
+
+  if (warp == 8) {
+    // =========================== TMA producer ===========================
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsOther));
+    if (lane == 0) {
+      mbar_expect_tx(&sm.q_full, 2 * kTileBytes);
+#pragma unroll
+      for (int t = 0; t < 2; ++t) {
+        tma_load_3d(sm.q[t], &tm_q, &sm.q_full, 0, hq0 + t, q_beg + q0);
+        tma_load_3d(sm.q[t] + kBoxBytes, &tm_q, &sm.q_full, 64, hq0 + t, q_beg + q0);
+      }
+      const int32_t* pt = p.page_table + ((int64_t)p.batch_mapping[b] * p.HKV + hkv) * p.NLP;
+      for (int n = 0; n < 2 * n_tiles; ++n) {
+        const int j = n >> 1;
+        const bool is_v = n & 1;
+        const int slot = n % kSlots;
+        const uint32_t ph = (n / kSlots) & 1;
+        const bool pre = j < n_pre;
+        int row;
+        if (pre) {
+          const int t0 = j * kBN;
+          const int pg = t0 / p.PS;
+          row = pt[pg] * p.PS + (t0 - pg * p.PS);
+        } else {
+          row = q_beg + (j - n_pre) * kBN;
+        }
+        mbar_wait(&sm.empty[slot], ph ^ 1);
+        mbar_expect_tx(&sm.full[slot], kTileBytes);
+        unsigned char* dst = sm.kv[slot];
+        if (pre) {
+          const CUtensorMap* m = is_v ? &tm_vc : &tm_kc;
+          tma_load_2d(dst, m, &sm.full[slot], 0, row);
+          tma_load_2d(dst + kBoxBytes, m, &sm.full[slot], 64, row);
+        } else {
+          const CUtensorMap* m = is_v ? &tm_v : &tm_k;
+          tma_load_3d(dst, m, &sm.full[slot], 0, hkv, row);
+          tma_load_3d(dst + kBoxBytes, m, &sm.full[slot], 64, hkv, row);
+        }
+      }
+    }
+  } else if (warp == 9) {
+    // ============================ UMMA issuer ============================
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsOther));
+    constexpr uint32_t idesc_qk = umma_idesc(BF16, kBM, kBN, false, false);
+    constexpr uint32_t idesc_pv = umma_idesc(BF16, kBM, kHD, false, true);
+
+    auto slot_of = [](int n) { return n % kSlots; };
+    auto phase_of = [](int n) { return (uint32_t)((n / kSlots) & 1); };
+
+    // S_t = Q_t . K_j^T  (K_j in ring entry 2j, already waited for)
+    auto issue_qk = [&](int t, int j) {
+      if (lane == 0) {
+        const uint32_t q_addr = smem_u32(sm.q[t]);
+        const uint32_t k_addr = smem_u32(sm.kv[slot_of(2 * j)]);
+        const uint32_t s_tmem = tmem + t * kBN;
+#pragma unroll
+        for (int kk = 0; kk < kHD / 16; ++kk) {
+          const uint32_t off = (kk >> 2) * kBoxBytes + (kk & 3) * 32;
+          umma_ss(s_tmem, umma_smem_desc(q_addr + off, 16, 1024), umma_smem_desc(k_addr + off, 16, 1024),
+                  idesc_qk, kk > 0 ? 1u : 0u);
+        }
+        umma_commit(&sm.s_full[t]);
+        if (t == 1) umma_commit(&sm.empty[slot_of(2 * j)]);  // K_j consumed by both heads
+      }
+      __syncwarp();
+    };
+    // O_t += P_t . V_j  (V_j in ring entry 2j + 1, already waited for)
+    auto issue_pv = [&](int t, int j) {
+      mbar_wait(&sm.p_full[t], j & 1);
+      tc_fence_after();
+      if (lane == 0) {
+        const uint32_t v_addr = smem_u32(sm.kv[slot_of(2 * j + 1)]);
+        const uint32_t p_tmem = tmem + t * kBN;
+        const uint32_t o_tmem = tmem + 256 + t * kHD;
+#pragma unroll
+        for (int kk = 0; kk < kBN / 16; ++kk) {
+          const uint64_t vdesc = umma_smem_desc(v_addr + kk * 2048, kBoxBytes, 1024);
+          umma_ts(o_tmem, p_tmem + kk * 8, vdesc, idesc_pv, (j > 0 || kk > 0) ? 1u : 0u);
+        }
+        if (t == 1) umma_commit(&sm.empty[slot_of(2 * j + 1)]);  // V_j consumed by both heads
+        umma_commit(&sm.o_done[t]);
+        if (j == n_tiles - 1) umma_commit(&sm.o_final[t]);
+      }
+      __syncwarp();
+    };
+    auto wait_v = [&](int j) {
+      const int n = 2 * j + 1;
+      mbar_wait(&sm.full[slot_of(n)], phase_of(n));
+      if (j == n_pre - 1 && (Lc % kBN) != 0) {
+        // ragged last prefix tile: rows >= Lc % 128 of the page are uninitialised memory; P is
+        // exactly 0 there but 0 * NaN would poison O, so zero those V rows.
+        const int valid = Lc % kBN;
+        uint4* v4 = reinterpret_cast<uint4*>(sm.kv[slot_of(n)]);
+        const uint4 z = make_uint4(0, 0, 0, 0);
+        for (int idx = lane; idx < (kBN - valid) * 16; idx += 32) {
+          const int r = valid + idx / 16, c = idx % 16;  // 16 x 16B per row across the 2 boxes
+          v4[(c >> 3) * (kBoxBytes / 16) + r * 8 + (c & 7)] = z;
+        }
+        fence_proxy_async_smem();
+        __syncwarp();
+      }
+      tc_fence_after();
+    };
+    auto wait_k = [&](int j) {
+      const int n = 2 * j;
+      mbar_wait(&sm.full[slot_of(n)], phase_of(n));
+      tc_fence_after();
+    };
+
+    mbar_wait(&sm.q_full, 0);
+    wait_k(0);
+    issue_qk(0, 0);
+    issue_qk(1, 0);
+    for (int j = 0; j < n_tiles; ++j) {
+      const bool more = j + 1 < n_tiles;
+      wait_v(j);
+      issue_pv(0, j);
+      if (more) {
+        wait_k(j + 1);
+        issue_qk(0, j + 1);
+      }
+      issue_pv(1, j);
+      if (more) issue_qk(1, j + 1);
+    }
+  } else if (warp < 8) {
+    // ====================== softmax / correction / epilogue ======================
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kRegsSoftmax));
+    const int t = warp >> 2;        // which head of the pair
+    const int quad = warp & 3;      // TMEM lane quadrant this warp may touch
+    const int row = quad * 32 + lane;
+    const uint32_t lane_base = (uint32_t)(quad * 32) << 16;
+    const bool row_valid = (q0 + row) < La;
+    const uint32_t s_tmem = tmem + t * kBN + lane_base;
+    const uint32_t o_tmem = tmem + 256 + t * kHD + lane_base;
+    float m_ref = -INFINITY, l = 0.f;
+
+    for (int j = 0; j < n_tiles; ++j) {
+      mbar_wait(&sm.s_full[t], j & 1);
+      tc_fence_after();
+      float s[kBN];
+#pragma unroll
+      for (int c = 0; c < kBN / 32; ++c) {
+        uint32_t tmp[32];
+        tmem_ld32(s_tmem + c * 32, tmp);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) s[c * 32 + i] = __uint_as_float(tmp[i]);
+      }
+      tc_wait_ld();
+
+      // ---- masks (boundary tiles only) ----
+      if (j < n_pre) {
+        const int valid = Lc - j * kBN;
+        if (valid < kBN) {
+#pragma unroll
+          for (int c = 0; c < kBN; ++c)
+            if (c >= valid) s[c] = -INFINITY;
+        }
+      } else if (j == n_tiles - 1) {
+#pragma unroll
+        for (int c = 0; c < kBN; ++c)
+          if (c > row) s[c] = -INFINITY;
+      }
+
+      float mx0 = s[0], mx1 = s[1], mx2 = s[2], mx3 = s[3];
+#pragma unroll
+      for (int c = 4; c < kBN; c += 4) {
+        mx0 = fmaxf(mx0, s[c]);
+        mx1 = fmaxf(mx1, s[c + 1]);
+        mx2 = fmaxf(mx2, s[c + 2]);
+        mx3 = fmaxf(mx3, s[c + 3]);
+      }
+      const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
+      const float m_new = fmaxf(m_ref, mx * p.scale_log2);
+      const bool need = (j == 0) || (m_new > m_ref + p.rescale_threshold);
+      if (__any_sync(0xffffffffu, need)) {
+        const float alpha = ex2(m_ref - m_new);  // m_ref == -inf on the first tile -> 0
+        m_ref = m_new;
+        l *= alpha;
+        if (j > 0) {
+          // O holds PV(0..j-1); PV(j-1) may still be in flight
+          mbar_wait(&sm.o_done[t], (j - 1) & 1);
+          tc_fence_after();
+#pragma unroll
+          for (int c = 0; c < kHD / 32; ++c) {
+            uint32_t o[32];
+            tmem_ld32(o_tmem + c * 32, o);
+            tc_wait_ld();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+            tmem_st32(o_tmem + c * 32, o);
+          }
+        }
+      }
+
+      // ---- P = exp2(S*scale - m_ref), row sum, 16-bit pack, back to TMEM over S ----
+      const float neg_m = (m_ref == -INFINITY) ? 0.f : -m_ref;
+      float l0 = 0.f, l1 = 0.f;
+#pragma unroll
+      for (int c = 0; c < kBN / 32; ++c) {
+        uint32_t pk[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const float p0 = ex2(fmaf(s[c * 32 + 2 * i], p.scale_log2, neg_m));
+          const float p1 = ex2(fmaf(s[c * 32 + 2 * i + 1], p.scale_log2, neg_m));
+          l0 += p0;
+          l1 += p1;
+          pk[i] = pack2<BF16>(p0, p1);
+        }
+        tmem_st16(s_tmem + c * 16, pk);
+      }
+      l += l0 + l1;
+      tc_wait_st();
+      tc_fence_before();
+      mbar_arrive(&sm.p_full[t]);
+    }
+
+    // ---- epilogue: O / l -> out ----
+    mbar_wait(&sm.o_final[t], 0);
+    tc_fence_after();
+    const float inv = l > 0.f ? 1.f / l : 0.f;
+    char* orow = reinterpret_cast<char*>(p.out) +
+                 ((int64_t)(q_beg + q0 + row) * p.o_stride_n + (int64_t)(hq0 + t) * kHD) * 2;
+#pragma unroll
+    for (int c = 0; c < kHD / 32; ++c) {
+      uint32_t o[32];
+      tmem_ld32(o_tmem + c * 32, o);
+      tc_wait_ld();
+      if (row_valid) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          uint4 w;
+          w.x = pack2<BF16>(__uint_as_float(o[8 * i + 0]) * inv, __uint_as_float(o[8 * i + 1]) * inv);
+          w.y = pack2<BF16>(__uint_as_float(o[8 * i + 2]) * inv, __uint_as_float(o[8 * i + 3]) * inv);
+          w.z = pack2<BF16>(__uint_as_float(o[8 * i + 4]) * inv, __uint_as_float(o[8 * i + 5]) * inv);
+          w.w = pack2<BF16>(__uint_as_float(o[8 * i + 6]) * inv, __uint_as_float(o[8 * i + 7]) * inv);
+          *reinterpret_cast<uint4*>(orow + c * 64 + i * 16) = w;
+        }
+      }
+    }
+  }
+
+  else {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsOther));  // warps 10, 11
+  }
+
+  // ---------------- teardown ----------------
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 9) tmem_dealloc(tmem, 512);
+}
+
+}  // namespace cvllm
+
+using namespace cvllm;
+
+// Launch the paired-head kernel.  Called by cvllm_prefill_attention (prefill_attn.cu) after the
+// argument checks and tensor-map construction; returns a CVLLM_* code.
+int cvllm_launch_prefill2(const CUtensorMap& tm_q, const CUtensorMap& tm_k, const CUtensorMap& tm_v,
+                          const CUtensorMap& tm_kc, const CUtensorMap& tm_vc, void* out,
+                          const int32_t* seq_lens_bh, const int32_t* page_table,
+                          const int32_t* batch_mapping, const int32_t* cu_seqlens_q, int B, int HQ,
+                          int HKV, int PS, int NLP, int64_t o_stride_n, int max_seqlen_q,
+                          float scale_log2, float rescale_threshold, bool bf16, cudaStream_t st) {
+  Prefill2Params p;
+  p.out = out; p.seq_lens_bh = seq_lens_bh; p.page_table = page_table;
+  p.batch_mapping = batch_mapping; p.cu_seqlens_q = cu_seqlens_q;
+  p.B = B; p.HQ = HQ; p.HKV = HKV; p.G = HQ / HKV; p.PS = PS; p.NLP = NLP;
+  p.o_stride_n = o_stride_n;
+  p.scale_log2 = scale_log2;
+  p.rescale_threshold = rescale_threshold;
+  const size_t smem = sizeof(Prefill2Smem) + 1024;
+  const dim3 grid((max_seqlen_q + p2::kBM - 1) / p2::kBM, HQ / 2, B);
+  static bool attr_set = false;
+  if (!attr_set) {
+    CVLLM_CHECK_CUDA(cudaFuncSetAttribute(prefill_attn2_kernel<true>,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CVLLM_CHECK_CUDA(cudaFuncSetAttribute(prefill_attn2_kernel<false>,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr_set = true;
+  }
+  if (bf16) prefill_attn2_kernel<true><<<grid, p2::kThreads, smem, st>>>(tm_q, tm_k, tm_v, tm_kc, tm_vc, p);
+  else prefill_attn2_kernel<false><<<grid, p2::kThreads, smem, st>>>(tm_q, tm_k, tm_v, tm_kc, tm_vc, p);
+  CVLLM_CHECK_LAUNCH();
+  return CVLLM_OK;
+}
+
+// debug aid (not part of include/cvllm.h): launch-relevant attributes of the paired kernel
+extern "C" int cvllm_debug_prefill2_attrs(int* out) {
+  cudaFuncAttributes a;
+  if (cudaFuncGetAttributes(&a, prefill_attn2_kernel<true>) != cudaSuccess) return -1;
+  out[0] = a.numRegs; out[1] = a.maxThreadsPerBlock; out[2] = (int)a.sharedSizeBytes;
+  out[3] = a.maxDynamicSharedSizeBytes; out[4] = (int)a.localSizeBytes; out[5] = (int)a.constSizeBytes;
+  out[6] = (int)(sizeof(Prefill2Smem) + 1024);
+  int dev = 0, v = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+  out[7] = v;
+  return 0;
+}

@@ -219,10 +219,20 @@ __global__ void __launch_bounds__(kLevThreads, 2) leverage_gram_kernel(const Lev
 struct EigSmem {
   float g[kSk][kSk + 1];
   float v[kSk][kSk + 1];
-  float rot_c[kSk / 2], rot_s[kSk / 2];
-  int pair_p[kSk / 2], pair_q[kSk / 2];
+  float4 rot[kSk / 2];  // (c, s, p, q) of each pair; p, q as int bit patterns
   int any_rot;
 };
+
+__device__ __forceinline__ float rcp_approx(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float sqrt_approx(float x) {
+  float y;
+  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 
 template <bool BF16>
 __global__ void __launch_bounds__(kEigThreads) leverage_eig_kernel(const float* __restrict__ gram,
@@ -242,7 +252,12 @@ __global__ void __launch_bounds__(kEigThreads) leverage_eig_kernel(const float* 
   if (tid == 0) sm.any_rot = 0;
   __syncthreads();
 
-  constexpr int NP = kSk / 2;  // 24 pairs
+  constexpr int NP = kSk / 2;       // 24 pairs
+  constexpr int SUB = 5;            // threads per pair-row: 24 * 5 = 120 workers
+  constexpr int JB = (NP + SUB - 1) / SUB;   // <= 5 column pairs per worker
+  constexpr int VR = (kSk + SUB - 1) / SUB;  // <= 10 V rows per worker
+  const int wi = tid / SUB, sub = tid - wi * SUB;
+  const bool worker = tid < NP * SUB;
   for (int sweep = 0; sweep < kJacobiSweeps; ++sweep) {
     for (int rnd = 0; rnd < kSk - 1; ++rnd) {
       if (tid < NP) {
@@ -255,37 +270,65 @@ __global__ void __launch_bounds__(kEigThreads) leverage_eig_kernel(const float* 
         const float app = sm.g[pp][pp], aqq = sm.g[qq][qq], apq = sm.g[pp][qq];
         float c = 1.f, s = 0.f;
         if (fabsf(apq) > 1e-30f) {
-          const float tau = (aqq - app) / (2.f * apq);
-          const float t = (tau >= 0.f ? 1.f : -1.f) / (fabsf(tau) + sqrtf(1.f + tau * tau));
-          c = rsqrtf(1.f + t * t);
+          // the rotation only has to be orthogonal (c^2 + s^2 = 1 to an ulp: c = rsqrt(1 + t^2),
+          // s = t c), not the exact annihilator: approximate rcp / sqrt keep the chain short
+          const float tau = (aqq - app) * 0.5f * rcp_approx(apq);
+          const float t = copysignf(rcp_approx(fabsf(tau) + sqrt_approx(fmaf(tau, tau, 1.f))), tau);
+          c = rsqrtf(fmaf(t, t, 1.f));
           s = t * c;
           // still moving? (below this the rotation is the identity in fp32)
-          if (fabsf(apq) > 1e-7f * sqrtf(fabsf(app * aqq))) sm.any_rot = 1;
+          if (apq * apq > 1e-14f * fabsf(app * aqq)) sm.any_rot = 1;
         }
-        sm.rot_c[tid] = c; sm.rot_s[tid] = s; sm.pair_p[tid] = pp; sm.pair_q[tid] = qq;
+        sm.rot[tid] = make_float4(c, s, __int_as_float(pp), __int_as_float(qq));
       }
       __syncthreads();
-      // G blocks (i, j): rows {p_i, q_i} x cols {p_j, q_j}
-      for (int it = tid; it < NP * NP; it += kEigThreads) {
-        const int i = it / NP, j = it - i * NP;
-        const int pi = sm.pair_p[i], qi = sm.pair_q[i], pj = sm.pair_p[j], qj = sm.pair_q[j];
-        const float ci = sm.rot_c[i], si = sm.rot_s[i], cj = sm.rot_c[j], sj = sm.rot_s[j];
-        const float gpp = sm.g[pi][pj], gpq = sm.g[pi][qj], gqp = sm.g[qi][pj], gqq = sm.g[qi][qj];
-        const float rpp = ci * gpp - si * gqp, rpq = ci * gpq - si * gqq;  // J_i^T . (rows)
-        const float rqp = si * gpp + ci * gqp, rqq = si * gpq + ci * gqq;
-        sm.g[pi][pj] = cj * rpp - sj * rpq;                                // . J_j (columns)
-        sm.g[pi][qj] = sj * rpp + cj * rpq;
-        sm.g[qi][pj] = cj * rqp - sj * rqq;
-        sm.g[qi][qj] = sj * rqp + cj * rqq;
-      }
-      // V <- V J
-      for (int it = tid; it < NP * kSk; it += kEigThreads) {
-        const int i = it / kSk, row = it - i * kSk;
-        const int pi = sm.pair_p[i], qi = sm.pair_q[i];
-        const float c = sm.rot_c[i], s = sm.rot_s[i];
-        const float vp = sm.v[row][pi], vq = sm.v[row][qi];
-        sm.v[row][pi] = c * vp - s * vq;
-        sm.v[row][qi] = s * vp + c * vq;
+      if (worker) {
+        // every load first (the in-place stores below would otherwise serialise the iterations)
+        const float4 ri = sm.rot[wi];
+        const int pi = __float_as_int(ri.z), qi = __float_as_int(ri.w);
+        float4 rj[JB];
+        float gpp[JB], gpq[JB], gqp[JB], gqq[JB];
+#pragma unroll
+        for (int u = 0; u < JB; ++u) {
+          const int j = sub + SUB * u;
+          if (j < NP) {
+            rj[u] = sm.rot[j];
+            const int pj = __float_as_int(rj[u].z), qj = __float_as_int(rj[u].w);
+            gpp[u] = sm.g[pi][pj]; gpq[u] = sm.g[pi][qj];
+            gqp[u] = sm.g[qi][pj]; gqq[u] = sm.g[qi][qj];
+          }
+        }
+        float vp[VR], vq[VR];
+#pragma unroll
+        for (int u = 0; u < VR; ++u) {
+          const int row = sub + SUB * u;
+          if (row < kSk) { vp[u] = sm.v[row][pi]; vq[u] = sm.v[row][qi]; }
+        }
+        const float ci = ri.x, si = ri.y;
+        // G blocks (wi, j): rows {p_i, q_i} x cols {p_j, q_j}:  J_i^T . G . J_j
+#pragma unroll
+        for (int u = 0; u < JB; ++u) {
+          const int j = sub + SUB * u;
+          if (j < NP) {
+            const int pj = __float_as_int(rj[u].z), qj = __float_as_int(rj[u].w);
+            const float cj = rj[u].x, sj = rj[u].y;
+            const float rpp = ci * gpp[u] - si * gqp[u], rpq = ci * gpq[u] - si * gqq[u];
+            const float rqp = si * gpp[u] + ci * gqp[u], rqq = si * gpq[u] + ci * gqq[u];
+            sm.g[pi][pj] = cj * rpp - sj * rpq;
+            sm.g[pi][qj] = sj * rpp + cj * rpq;
+            sm.g[qi][pj] = cj * rqp - sj * rqq;
+            sm.g[qi][qj] = sj * rqp + cj * rqq;
+          }
+        }
+        // V <- V J_i
+#pragma unroll
+        for (int u = 0; u < VR; ++u) {
+          const int row = sub + SUB * u;
+          if (row < kSk) {
+            sm.v[row][pi] = ci * vp[u] - si * vq[u];
+            sm.v[row][qi] = si * vp[u] + ci * vq[u];
+          }
+        }
       }
       __syncthreads();
     }

@@ -234,26 +234,47 @@ __global__ void __launch_bounds__(kPassThreads) sel_resolve_kernel(const float* 
   if (tid == 0) { s_btile = -1; s_before = 0; }
   __syncthreads();
   if (sg.active) {
-    // boundary tile: the one holding the `remaining`-th tie in flat order (serial over <= len/256 tiles)
-    if (tid == 0) {
-      uint32_t run = 0;
-      int bt = tiles_b;  // all ties taken
-      for (int t = 0; t < tiles_b; ++t) {
+    // boundary tile: the first one whose cumulative tie count (flat order) exceeds `remaining`
+    {
+      const int lane = tid & 31, warp = tid >> 5;
+      uint32_t carry = 0;
+      if (tid == 0) s_btile = tiles_b;  // default: every tie is taken
+      __syncthreads();
+      for (int base = 0; base < tiles_b; base += kPassThreads) {
+        const int t = base + tid;
         uint32_t c = 0;
-        for (int h = 0; h < H; ++h) c += tt[t * H + h];
-        if (run + c > sg.remaining) { bt = t; break; }
-        run += c;
+        if (t < tiles_b)
+          for (int h = 0; h < H; ++h) c += tt[t * H + h];
+        // block-wide exclusive prefix of c
+        uint32_t incl = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const uint32_t x = __shfl_up_sync(0xffffffffu, incl, o);
+          if (lane >= o) incl += x;
+        }
+        if (lane == 31) s_warp[warp] = (int)incl;
+        __syncthreads();
+        uint32_t wbase = 0, total = 0;
+        for (int wv = 0; wv < kPassThreads / 32; ++wv) {
+          if (wv < warp) wbase += (uint32_t)s_warp[wv];
+          total += (uint32_t)s_warp[wv];
+        }
+        const uint32_t run = carry + wbase + incl - c;
+        if (t < tiles_b && run <= sg.remaining && run + c > sg.remaining) {
+          s_btile = t;  // unique: the prefix is monotone
+          s_before = run;
+        }
+        carry += total;
+        __syncthreads();
       }
-      s_btile = bt;
-      s_before = run;
+      if (tid == 0 && s_btile == tiles_b) s_before = carry;
+      __syncthreads();
     }
-    __syncthreads();
     const int bt = s_btile;
     // whole tiles before the boundary: all their ties are taken
-    if (tid < H) {
-      uint32_t c = 0;
-      for (int t = 0; t < min(bt, tiles_b); ++t) c += tt[t * H + tid];
-      s_tiesel[tid] = c;
+    for (int i = tid; i < min(bt, tiles_b) * H; i += kPassThreads) {
+      const uint32_t c = tt[i];
+      if (c) atomicAdd(&s_tiesel[i % H], c);
     }
     __syncthreads();
     if (bt < tiles_b) {

@@ -53,8 +53,10 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
     if (++spins > CVLLM_MBAR_SPIN_LIMIT) {
+#ifdef CVLLM_MBAR_DEBUG  // a printf call here makes every live register around a wait spill-able
       printf("cvllm: mbarrier timeout block(%d,%d,%d) thread %d bar@%u parity %u\n", blockIdx.x,
              blockIdx.y, blockIdx.z, threadIdx.x, smem_u32(bar), parity);
+#endif
       __trap();
     }
   }

@@ -14,6 +14,18 @@ ATOL = {torch.float16: 3e-3, torch.bfloat16: 2e-2}  # reference test atol (fp16)
 REL = {torch.float16: 2e-3, torch.bfloat16: 1e-2}
 
 
+@pytest.fixture(autouse=True, params=["paired", "single"])
+def kernel_variant(request, monkeypatch):
+    """Every test runs on both tcgen05 kernels: 'paired' = two query heads of a KV head per CTA
+    (prefill_attn2.cu, the default for even GQA groups), 'single' = one head per CTA (prefill_attn.cu,
+    the path odd groups take), forced through the library's CVLLM_PREFILL_V1 switch."""
+    if request.param == "single":
+        monkeypatch.setenv("CVLLM_PREFILL_V1", "1")
+    else:
+        monkeypatch.delenv("CVLLM_PREFILL_V1", raising=False)
+    return request.param
+
+
 def _run(q, k, v, kc, vc, lens, pt, bm, cu, HKV, PS, scale=None):
     seqlens = cu[1:] - cu[:-1]
     out = causal_sparse_varlen_with_cache(q, k, v, kc, vc, lens, pt, bm, cu, int(seqlens.max()), int(lens.max()),
