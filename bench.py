@@ -384,6 +384,46 @@ def workload_config() -> dict:
     }
 
 
+class Ranks:
+    """The harness's only use of torch.distributed: a barrier and max / sum reductions over the
+    ranks (NCCL on GPUs, gloo in the CPU tests).  The measured path itself has no collective."""
+
+    def __init__(self, world: int, device, backend: str | None = None, init: bool = True):
+        self.world, self.device, self.dist = world, torch.device(device), None
+        if world > 1:
+            import torch.distributed as dist
+            self.dist = dist
+            if init and not dist.is_initialized():
+                if backend is None:
+                    backend = "nccl" if self.device.type == "cuda" else "gloo"
+                kw = {"device_id": self.device} if backend == "nccl" else {}
+                dist.init_process_group(backend, **kw)
+            self._owns = init
+
+    def barrier(self):
+        if self.dist is not None:
+            self.dist.barrier()
+        if self.device.type == "cuda":
+            torch.cuda.synchronize()
+
+    def _reduce(self, x: float, op) -> float:
+        if self.dist is None:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=self.device)
+        self.dist.all_reduce(t, op=op)
+        return float(t.item())
+
+    def max(self, x: float) -> float:
+        return self._reduce(x, self.dist.ReduceOp.MAX) if self.dist is not None else x
+
+    def sum(self, x: float) -> float:
+        return self._reduce(x, self.dist.ReduceOp.SUM) if self.dist is not None else x
+
+    def close(self):
+        if self.dist is not None and getattr(self, "_owns", False) and self.dist.is_initialized():
+            self.dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -404,29 +444,8 @@ def main():
     assert torch.cuda.is_available(), "bench.py needs a CUDA device (there is no CPU fallback)"
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=dev)
-
-    def barrier():
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def max_over_ranks(x: float) -> float:
-        if dist is None:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
-    def sum_over_ranks(x: float) -> float:
-        if dist is None:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        return float(t.item())
+    ranks = Ranks(world, dev)
+    barrier, max_over_ranks, sum_over_ranks = ranks.barrier, ranks.max, ranks.sum
 
     from compactor_vllm import _native as N
     lib = N.lib()
@@ -588,8 +607,7 @@ def main():
             "e2e": e2e, "gpu_launches": total_launches, "clocks": clocks,
         }
         print(json.dumps(line), flush=True)
-    if dist is not None:
-        dist.destroy_process_group()
+    ranks.close()
 
 
 if __name__ == "__main__":

@@ -1,35 +1,39 @@
-"""Compression registry (reference: compression/__init__.py:13-39)."""
-from compactor_vllm.compression.common import BaseCompressionMethod, NoCompression
-from compactor_vllm.compression.compactor import CompactorCompression
-from compactor_vllm.compression.compression_config import (
-    BatchCompressionParams,
-    CompressionMethod,
-    SequenceCompressionParams,
-)
-from compactor_vllm.compression.snapkv import SnapKVCompression
+"""Scorer plugins keyed by CompressionMethod, and the two hooks the model code calls around RoPE.
 
-COMPRESSION_REGISTRY: dict[CompressionMethod, type[BaseCompressionMethod]] = {
-    CompressionMethod.COMPACTOR: CompactorCompression,
-    CompressionMethod.SNAPKV: SnapKVCompression,
-    CompressionMethod.NONE: NoCompression,
+Boundary mirrored: the reference's compression/__init__.py:13-29 (`COMPRESSION_REGISTRY`,
+`apply_prerope_compression`, `apply_postrope_compression`).
+"""
+from compactor_vllm.api_types import BatchCompressionParams, CompressionMethod, SequenceCompressionParams
+from compactor_vllm.compression import common as _common
+from compactor_vllm.compression import compactor as _compactor
+from compactor_vllm.compression import snapkv as _snapkv
+
+COMPRESSION_REGISTRY = {
+    CompressionMethod.NONE: _common.NoCompression,
+    CompressionMethod.SNAPKV: _snapkv.SnapKVCompression,
+    CompressionMethod.COMPACTOR: _compactor.CompactorCompression,
 }
 
 
+def _plugin(context):
+    return COMPRESSION_REGISTRY[context.compression_context.compression_method]
+
+
 def apply_prerope_compression(q, k, v, context):
-    method = context.compression_context.compression_method
-    return COMPRESSION_REGISTRY[method].pre_rope_scoring(q, k, v, context=context)
+    """Scores that only need pre-RoPE tensors (COMPACTOR: leverage sketch of K); None otherwise."""
+    return _plugin(context).pre_rope_scoring(q, k, v, context=context)
 
 
 def apply_postrope_compression(q, k, v, prerope_scores, context):
-    method = context.compression_context.compression_method
-    return COMPRESSION_REGISTRY[method].post_rope_scoring(q, k, v, prerope_scores, context=context)
+    """Final [N, HKV] fp32 scores (or None) from post-RoPE q / k and the pre-RoPE partial scores."""
+    return _plugin(context).post_rope_scoring(q, k, v, prerope_scores, context=context)
 
 
 __all__ = [
+    "COMPRESSION_REGISTRY",
     "apply_prerope_compression",
     "apply_postrope_compression",
-    "CompressionMethod",
     "BatchCompressionParams",
+    "CompressionMethod",
     "SequenceCompressionParams",
-    "COMPRESSION_REGISTRY",
 ]

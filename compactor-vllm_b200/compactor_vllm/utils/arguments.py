@@ -33,3 +33,14 @@ def tokens_to_retain(
 def max_tokens_to_retain(prompt_lens: Sequence[int], num_kv_heads_local: int) -> int:
     """top_k handed to the ranking = max(context_lens)*HKV_local  (:208-211)."""
     return max(prompt_lens) * num_kv_heads_local
+
+
+def kv_head_shard(rank: int, world_size: int, num_heads: int, num_kv_heads: int):
+    """Heads owned by tensor-parallel rank `rank`: KV head h and its G query heads live on rank
+    h // (HKV / tp)  (reference: models/llama3.py:41-50, core/memory_manager.py:29-32).
+    Returns (kv_start, kv_end, q_start, q_end), end-exclusive."""
+    assert num_kv_heads % world_size == 0, "world size needs to divide num_kv_heads"
+    assert num_heads % num_kv_heads == 0
+    per = num_kv_heads // world_size
+    group = num_heads // num_kv_heads
+    return rank * per, (rank + 1) * per, rank * per * group, (rank + 1) * per * group

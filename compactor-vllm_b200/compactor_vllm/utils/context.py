@@ -1,69 +1,82 @@
-"""Process-global per-step context (reference: utils/context.py:10-83)."""
-from dataclasses import dataclass
-from typing import List
+"""Per-step state shared between the runner and the attention / compression code.
 
-import torch
-from compactor_vllm.compression.compression_config import CompressionMethod
+The reference keeps one module-global `Context` (utils/context.py:10-83) that the runner replaces
+before every forward pass; models and `Attention.forward` read it through `get_context()`.  Same
+surface here (`Context`, `CompressionContext`, `get_context`, `set_context`, `reset_context`, same
+field names), built from one field table so the two stay in step.
+"""
+from __future__ import annotations
+
+from types import SimpleNamespace
+from typing import Any
+
+from compactor_vllm.api_types import CompressionMethod
 from compactor_vllm.config.engine_config import AttentionBackend
 
+_COMPRESSION_FIELDS: dict[str, Any] = {
+    "compression_method": CompressionMethod.COMPACTOR,
+    "compression_chunk_size": -1,        # leverage-score chunk (tokens); -1 = whole sequence
+    "batch_tokens_to_retain": None,      # int32 [B] device tensor: (token, head) pairs kept per sequence
+    "max_tokens_to_retain": 0,           # max_len * HKV_local
+    "context_lens": None,                # host list [B]
+    "PHI": None,                         # [D, sketch] Gaussian sketch, model dtype
+    "protected_first_tokens": None,      # host list [B]
+    "protected_last_tokens": None,       # host list [B]
+}
 
-@dataclass
-class CompressionContext:
-    compression_method: CompressionMethod = CompressionMethod.COMPACTOR
-    compression_chunk_size: int = -1
-    batch_tokens_to_retain: torch.Tensor | None = None
-    max_tokens_to_retain: int = 0
-    context_lens: List[int] | None = None
-    PHI: torch.Tensor | None = None
-    protected_first_tokens: List[int] | None = None
-    protected_last_tokens: List[int] | None = None
-
-
-@dataclass
-class Context:
-    is_prefill: bool = False
-    do_compression: bool = False
-    cu_seqlens_q: torch.Tensor | None = None
-    cu_seqlens_k: torch.Tensor | None = None
-    max_seqlen_q: int = 0
-    max_seqlen_k: int = 0
-    batch_mapping: torch.Tensor | None = None
-    max_bh_len: int = 0
-    compression_context: CompressionContext | None = None
-    STORE_STREAM: "torch.cuda.Stream | None" = None
-    key_split: int | None = None
-    attention_backend: AttentionBackend = AttentionBackend.COMPACTOR_TRITON
+_STEP_FIELDS: dict[str, Any] = {
+    "is_prefill": False,
+    "do_compression": False,
+    "cu_seqlens_q": None,
+    "cu_seqlens_k": None,
+    "max_seqlen_q": 0,
+    "max_seqlen_k": 0,
+    "batch_mapping": None,               # int32 [B]: batch row -> cache slot (slot 0 is reserved)
+    "max_bh_len": 0,
+    "compression_context": None,
+    "STORE_STREAM": None,                # side stream for scoring + store during prefill
+    "key_split": None,                   # decode split count fixed at CUDA-graph capture time
+    "attention_backend": AttentionBackend.COMPACTOR_TRITON,
+}
 
 
-_CONTEXT = Context()
+class _Record(SimpleNamespace):
+    _fields: dict[str, Any] = {}
+
+    def __init__(self, *args, **kwargs):
+        names = list(self._fields)
+        if len(args) > len(names):
+            raise TypeError(f"{type(self).__name__} takes at most {len(names)} positional arguments")
+        values = dict(self._fields)
+        values.update(zip(names, args))
+        for key, val in kwargs.items():
+            if key not in values:
+                raise TypeError(f"{type(self).__name__} has no field {key!r}")
+            values[key] = val
+        super().__init__(**values)
 
 
-def get_context():
-    return _CONTEXT
+class CompressionContext(_Record):
+    _fields = _COMPRESSION_FIELDS
 
 
-def set_context(
-    *,
-    is_prefill,
-    do_compression=False,
-    cu_seqlens_q=None,
-    cu_seqlens_k=None,
-    max_seqlen_q=0,
-    max_seqlen_k=0,
-    batch_mapping=None,
-    max_bh_len=0,
-    compression_context: CompressionContext = None,
-    STORE_STREAM=None,
-    key_split=None,
-    attention_backend=AttentionBackend.COMPACTOR_TRITON,
-):
-    global _CONTEXT
-    _CONTEXT = Context(
-        is_prefill, do_compression, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k,
-        batch_mapping, max_bh_len, compression_context, STORE_STREAM, key_split, attention_backend,
-    )
+class Context(_Record):
+    _fields = _STEP_FIELDS
 
 
-def reset_context():
-    global _CONTEXT
-    _CONTEXT = Context()
+_current = Context()
+
+
+def get_context() -> Context:
+    return _current
+
+
+def set_context(*, is_prefill, **step) -> None:
+    """Replace the global context; unspecified fields take their defaults."""
+    global _current
+    _current = Context(is_prefill=is_prefill, **step)
+
+
+def reset_context() -> None:
+    global _current
+    _current = Context()

@@ -235,7 +235,7 @@ __device__ __forceinline__ float sqrt_approx(float x) {
 }
 
 template <bool BF16>
-__global__ void __launch_bounds__(kEigThreads) leverage_eig_kernel(const float* __restrict__ gram,
+__global__ void __launch_bounds__(kEigThreads, 4) leverage_eig_kernel(const float* __restrict__ gram,
                                                                    float* __restrict__ sv_out,
                                                                    const int32_t* __restrict__ chunk_offsets,
                                                                    int HKV) {
@@ -252,12 +252,9 @@ __global__ void __launch_bounds__(kEigThreads) leverage_eig_kernel(const float* 
   if (tid == 0) sm.any_rot = 0;
   __syncthreads();
 
-  constexpr int NP = kSk / 2;       // 24 pairs
-  constexpr int SUB = 5;            // threads per pair-row: 24 * 5 = 120 workers
-  constexpr int JB = (NP + SUB - 1) / SUB;   // <= 5 column pairs per worker
-  constexpr int VR = (kSk + SUB - 1) / SUB;  // <= 10 V rows per worker
-  const int wi = tid / SUB, sub = tid - wi * SUB;
-  const bool worker = tid < NP * SUB;
+  constexpr int NP = kSk / 2;                                      // 24 pairs
+  constexpr int GB = (NP * NP + kEigThreads - 1) / kEigThreads;    // G blocks per thread (5)
+  constexpr int VB = (NP * kSk + kEigThreads - 1) / kEigThreads;   // V items per thread (9)
   for (int sweep = 0; sweep < kJacobiSweeps; ++sweep) {
     for (int rnd = 0; rnd < kSk - 1; ++rnd) {
       if (tid < NP) {
@@ -282,36 +279,46 @@ __global__ void __launch_bounds__(kEigThreads) leverage_eig_kernel(const float* 
         sm.rot[tid] = make_float4(c, s, __int_as_float(pp), __int_as_float(qq));
       }
       __syncthreads();
-      if (worker) {
-        // every load first (the in-place stores below would otherwise serialise the iterations)
-        const float4 ri = sm.rot[wi];
-        const int pi = __float_as_int(ri.z), qi = __float_as_int(ri.w);
-        float4 rj[JB];
-        float gpp[JB], gpq[JB], gqp[JB], gqq[JB];
+      {
+        // The kernel is bound by shared-memory wavefronts, so the item -> lane maps are chosen for
+        // the banks: G block (i, j) with j fastest (g[p_i][p_j] over distinct p_j: <= 2-way), V item
+        // (i, row) with row fastest (v[row][p_i], stride 49: conflict-free).  Every load is issued
+        // before the first in-place store (the stores would otherwise serialise the iterations).
+        float4 gi[GB], gj[GB];
+        float gpp[GB], gpq[GB], gqp[GB], gqq[GB];
 #pragma unroll
-        for (int u = 0; u < JB; ++u) {
-          const int j = sub + SUB * u;
-          if (j < NP) {
-            rj[u] = sm.rot[j];
-            const int pj = __float_as_int(rj[u].z), qj = __float_as_int(rj[u].w);
+        for (int u = 0; u < GB; ++u) {
+          const int it = tid + u * kEigThreads;
+          if (it < NP * NP) {
+            const int i = it / NP, j = it - i * NP;
+            gi[u] = sm.rot[i];
+            gj[u] = sm.rot[j];
+            const int pi = __float_as_int(gi[u].z), qi = __float_as_int(gi[u].w);
+            const int pj = __float_as_int(gj[u].z), qj = __float_as_int(gj[u].w);
             gpp[u] = sm.g[pi][pj]; gpq[u] = sm.g[pi][qj];
             gqp[u] = sm.g[qi][pj]; gqq[u] = sm.g[qi][qj];
           }
         }
-        float vp[VR], vq[VR];
+        float4 vi[VB];
+        float vp[VB], vq[VB];
 #pragma unroll
-        for (int u = 0; u < VR; ++u) {
-          const int row = sub + SUB * u;
-          if (row < kSk) { vp[u] = sm.v[row][pi]; vq[u] = sm.v[row][qi]; }
+        for (int u = 0; u < VB; ++u) {
+          const int it = tid + u * kEigThreads;
+          if (it < NP * kSk) {
+            const int i = it / kSk, row = it - i * kSk;
+            vi[u] = sm.rot[i];
+            vp[u] = sm.v[row][__float_as_int(vi[u].z)];
+            vq[u] = sm.v[row][__float_as_int(vi[u].w)];
+          }
         }
-        const float ci = ri.x, si = ri.y;
-        // G blocks (wi, j): rows {p_i, q_i} x cols {p_j, q_j}:  J_i^T . G . J_j
+        // G blocks: rows {p_i, q_i} x cols {p_j, q_j}:  J_i^T . G . J_j
 #pragma unroll
-        for (int u = 0; u < JB; ++u) {
-          const int j = sub + SUB * u;
-          if (j < NP) {
-            const int pj = __float_as_int(rj[u].z), qj = __float_as_int(rj[u].w);
-            const float cj = rj[u].x, sj = rj[u].y;
+        for (int u = 0; u < GB; ++u) {
+          const int it = tid + u * kEigThreads;
+          if (it < NP * NP) {
+            const int pi = __float_as_int(gi[u].z), qi = __float_as_int(gi[u].w);
+            const int pj = __float_as_int(gj[u].z), qj = __float_as_int(gj[u].w);
+            const float ci = gi[u].x, si = gi[u].y, cj = gj[u].x, sj = gj[u].y;
             const float rpp = ci * gpp[u] - si * gqp[u], rpq = ci * gpq[u] - si * gqq[u];
             const float rqp = si * gpp[u] + ci * gqp[u], rqq = si * gpq[u] + ci * gqq[u];
             sm.g[pi][pj] = cj * rpp - sj * rpq;
@@ -322,11 +329,13 @@ __global__ void __launch_bounds__(kEigThreads) leverage_eig_kernel(const float* 
         }
         // V <- V J_i
 #pragma unroll
-        for (int u = 0; u < VR; ++u) {
-          const int row = sub + SUB * u;
-          if (row < kSk) {
-            sm.v[row][pi] = ci * vp[u] - si * vq[u];
-            sm.v[row][qi] = si * vp[u] + ci * vq[u];
+        for (int u = 0; u < VB; ++u) {
+          const int it = tid + u * kEigThreads;
+          if (it < NP * kSk) {
+            const int i = it / kSk, row = it - i * kSk;
+            const float c = vi[u].x, s = vi[u].y;
+            sm.v[row][__float_as_int(vi[u].z)] = c * vp[u] - s * vq[u];
+            sm.v[row][__float_as_int(vi[u].w)] = s * vp[u] + c * vq[u];
           }
         }
       }
