@@ -271,7 +271,10 @@ def time_loop(fn, iters: int, flush=None) -> float:
     tot = 0.0
     for _ in range(iters):
         if flush is not None:
+            # cold AND clean L2: a 256 MB write leaves L2 full of dirty lines whose write-back the timed
+            # kernel would pay for (measured: +6..14 us on a 120 us decode), so it is followed by a 256 MB read
             flush.zero_()
+            flush.view(torch.float32).sum()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
         fn()
@@ -282,12 +285,14 @@ def time_loop(fn, iters: int, flush=None) -> float:
 
 
 def decode_bench(device, dtype, B: int, lens_bh: torch.Tensor, iters: int, flush, seed: int):
-    """decode_store_kv + head_sparse_decode_attention on a synthetic compacted cache; returns
-    (ms per step, algorithmic bytes per step)."""
+    """One decode step = decode_store_kv + head_sparse_decode_attention on a synthetic compacted cache,
+    captured in a CUDA graph and replayed (how the reference engine runs decode, core/model_runner.py:524-528);
+    every replay is timed with CUDA events after a cold-L2 flush.  Returns (ms per step, algorithmic bytes)."""
     from compactor_vllm.attention.sparse_decode_kernel import head_sparse_decode_attention
     from compactor_vllm.kv_cache.store_kv_cache import decode_store_kv
     g = torch.Generator().manual_seed(seed)
-    nlp = int((int(lens_bh.max()) + iters + 8 + PS - 1) // PS)
+    warm = 8
+    nlp = int((int(lens_bh.max()) + iters + warm + 8 + PS - 1) // PS)
     n_pages = (B + 1) * HKV * nlp
     pt = torch.randperm(n_pages, generator=g).to(torch.int32).view(B + 1, HKV, nlp).to(device)
     kc = torch.randn((n_pages * PS, D), device=device, dtype=dtype)
@@ -303,11 +308,21 @@ def decode_bench(device, dtype, B: int, lens_bh: torch.Tensor, iters: int, flush
                         v_cache=vc, PAGE_SIZE=PS)
         return head_sparse_decode_attention(q, kc, vc, lens, pt, bm, HKV, PS)
 
-    for _ in range(3):
-        step()
+    gs = torch.cuda.Stream(device=device)
+    gs.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(gs):
+        for _ in range(3):
+            step()  # workspaces of the capture stream
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=gs):
+            step()
     torch.cuda.synchronize()
-    ms = time_loop(step, iters, flush)
-    rows = int(lens_bh.sum()) + B * HKV * (3 + iters // 2)
+    for _ in range(warm - 4):
+        graph.replay()
+    torch.cuda.synchronize()
+    ms = time_loop(graph.replay, iters, flush)
+    rows = int(lens_bh.sum()) + B * HKV * (warm + iters // 2)
     nbytes = rows * D * 2 * 2 + B * HQ * D * 2 * 2 + B * HKV * D * 2 * 2 * 2
     return ms, nbytes
 
@@ -379,7 +394,7 @@ def workload_config() -> dict:
         "workload": f"M: 1 x {SEQ}-token sequence per rank, HQ={HQ} HKV={HKV} D={D} page={PS} bf16, "
                     f"COMPACTOR keep {int(RATIO * 100)}% (first {PROT_FIRST}/last {PROT_LAST} protected), "
                     "one layer's hot path per step",
-        "l2": "prefill inputs (470 MB) exceed the 126 MB L2; decode iterations flush L2 (256 MB write)",
+        "l2": "prefill inputs (470 MB) exceed the 126 MB L2; decode iterations flush L2 (256 MB write, then a 256 MB read so the flushed L2 holds no dirty lines)",
         "parallelism": "independent sequences per rank, no collective in the path",
     }
 
@@ -540,7 +555,7 @@ def main():
         comps["decode_b16_us"] = ms_d16 * 1e3
         roof_dec = {"bound": "hbm", "achieved": by_d16 / (ms_d16 * 1e-3) / 1e9, "peak": pk["hbm"], "unit": "GB/s",
                     "frac": by_d16 / (ms_d16 * 1e-3) / 1e9 / pk["hbm"], "traffic": None,
-                    "kernel": "decode_attn_kernel (B=16 ragged, mean 10240 rows/head)", "peak_src": pk["src"]}
+                    "kernel": "decode step (decode_store_kernel + decode_attn_kernel) replayed from a CUDA graph, B=16 ragged, mean 10240 rows/head", "peak_src": pk["src"]}
         del flush
 
         # ---------------- end to end: pinned host buffers in, host out ----------------

@@ -113,11 +113,15 @@ def dtype_code(dt: torch.dtype) -> int:
 _WORKSPACES: dict = {}
 
 
-def workspace(device: torch.device, nbytes: int, tag: str = "") -> torch.Tensor:
-    """Grow-only per-(device, stream, tag) byte scratch from torch's caching allocator."""
+def workspace(device: torch.device, nbytes: int, tag: str = "", zero: bool = False) -> torch.Tensor:
+    """Grow-only per-(device, stream, tag) byte scratch from torch's caching allocator.
+
+    zero=True: the buffer is zero-filled when it is (re)allocated — for kernels whose contract is
+    "control words zero on entry, restored to zero on exit" (decode attention's head tickets)."""
     key = (device.index, torch.cuda.current_stream(device).cuda_stream, tag)
     buf = _WORKSPACES.get(key)
     if buf is None or buf.numel() < nbytes:
-        buf = torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=device)
+        alloc = torch.zeros if zero else torch.empty
+        buf = alloc(max(int(nbytes), 256), dtype=torch.uint8, device=device)
         _WORKSPACES[key] = buf
     return buf

@@ -57,7 +57,9 @@ def head_sparse_decode_attention(
         return out
     L = N.lib()
     ws_bytes = L.cvllm_decode_attention_workspace_bytes(B, HQ, HKV, D, 0)
-    ws = N.workspace(dev, ws_bytes, "decode_attn")
+    # one workspace per (B, HQ, HKV): the ticket region's size depends on B*HKV, and the "zero on
+    # entry, zero on exit" contract only holds while the layout stays the same
+    ws = N.workspace(dev, ws_bytes, f"decode_attn:{B}:{HQ}:{HKV}", zero=True)
     rc = L.cvllm_decode_attention(
         N.ptr(q), N.ptr(out), N.ptr(k), N.ptr(v), N.ptr(seq_lens_bh), N.ptr(global_page_table),
         N.ptr(batch_mapping), N.ptr(ws), ws.numel(), B, HQ, HKV, D, int(PAGE_SIZE),

@@ -146,7 +146,13 @@ int cvllm_select_store_topk(const float* scores, int64_t s_stride_n,
  * (K2 :247-388 + K3 :392-435).  One query token per sequence against the
  * per-(b,h) paged rows; balanced split over 128-token units with an in-kernel
  * LSE merge.  Rows with L==0 are written as zeros.  `num_ctas` <= 0 picks
- * 2 * SM count.  Graph-capturable: no host sync, fixed grid. */
+ * one persistent CTA per SM.  PS must be 16, 32, 64 or a multiple of 128 (a
+ * TMA box of min(PS,128) rows never crosses a page).  Workspace contract: the
+ * first 256-byte-rounded B*HKV*4 bytes are per-head tickets that must be ZERO
+ * the first time a workspace is used; every launch leaves them zero again, so
+ * a workspace zeroed once at allocation can be reused forever (and a captured
+ * graph is the single kernel node).  Graph-capturable: no host sync, fixed
+ * grid. */
 size_t cvllm_decode_attention_workspace_bytes(int B, int HQ, int HKV, int D, int num_ctas);
 int cvllm_decode_attention(const void* q, void* out, const void* k_cache, const void* v_cache,
                            const int32_t* seq_lens_bh, const int32_t* page_table,

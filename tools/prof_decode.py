@@ -1,15 +1,21 @@
-"""A handful of decode steps (B=16 ragged, mean 10240 rows/head: BASELINE config 3's shape) for ncu."""
+"""A handful of decode launches (B=16 ragged, mean 10240 rows/head: BASELINE config 3's shape) for ncu."""
 import sys
 from pathlib import Path
 ROOT = Path(__file__).resolve().parent.parent
-sys.path[:0] = [str(ROOT), str(ROOT / "compactor-vllm_b200")]
+sys.path[:0] = [str(ROOT), str(ROOT / "compactor-vllm_b200"), str(ROOT / "tools")]
 import torch
-import bench
+from ref_compare import _paged, HQ, HKV, D, PS
+from compactor_vllm.attention.sparse_decode_kernel import head_sparse_decode_attention
 
 dev = torch.device("cuda", 0)
 torch.cuda.set_device(dev)
-flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
-g = torch.Generator().manual_seed(3)
-lens16 = ((torch.rand((16, bench.HKV), generator=g) + 0.5) * 10240).long()
-ms, nbytes = bench.decode_bench(dev, torch.bfloat16, 16, lens16, 5, flush, 6)
-print(f"decode B=16: {ms * 1e3:.1f} us, {nbytes / ms / 1e6:.1f} GB/s algorithmic")
+B, mean = 16, 10240
+gd = torch.Generator().manual_seed(11 + B)
+lens_bh = torch.randint(mean // 2, mean * 3 // 2 + 1, (B, HKV), generator=gd).to(torch.int32)
+kc, vc, pt, bm = _paged(torch, B, int(lens_bh.max()) + 64, 12 + B, dev)
+ld = lens_bh.to(dev)
+q = torch.randn((B, HQ, D), device=dev, dtype=torch.bfloat16)
+for _ in range(6):
+    out = head_sparse_decode_attention(q, kc, vc, ld, pt, bm, HKV, PS)
+torch.cuda.synchronize()
+print("ok", float(out.float().abs().mean()))

@@ -65,6 +65,17 @@ class Timer:
     def __init__(self, torch):
         self.torch = torch
         self.flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+        self.flush2 = torch.zeros(64 << 20, dtype=torch.float32, device="cuda")
+        self.flush_mode = "write"
+
+    def do_flush(self):
+        """"write": 256 MB memset (L2 left full of DIRTY lines whose write-back the timed kernel then pays);
+        "write+read": the memset followed by a 256 MB read, so L2 is cold but clean; "none"."""
+        if self.flush_mode == "none":
+            return
+        self.flush.zero_()
+        if self.flush_mode == "write+read":
+            self.flush2.sum()
 
     def __call__(self, fn, iters=10, warm=3, pre=None):
         torch = self.torch
@@ -77,7 +88,7 @@ class Timer:
         for _ in range(iters):
             if pre:
                 pre()
-            self.flush.zero_()
+            self.do_flush()
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record()
             fn()
@@ -104,7 +115,7 @@ class Timer:
         torch.cuda.synchronize()
         tot = 0.0
         for _ in range(iters):
-            self.flush.zero_()
+            self.do_flush()
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record()
             gr.replay()
