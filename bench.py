@@ -196,7 +196,8 @@ class Workload:
             max_tokens_to_retain=A.max_tokens_to_retain([n_tok], HKV), context_lens=[n_tok],
             PHI=A.make_phi(D, SKETCH, self.dtype, device), protected_first_tokens=[PROT_FIRST],
             protected_last_tokens=[PROT_LAST])
-        self.store_stream = torch.cuda.Stream(device=device)
+        # the engine's STORE_STREAM (core/model_runner.py); high priority: its short kernels get SMs as attention CTAs retire (CVLLM_STORE_PRIO=0 for the reference default)
+        self.store_stream = torch.cuda.Stream(device=device, priority=int(os.environ.get("CVLLM_STORE_PRIO", "-1")))
         self.attn_events = []  # (start, end) around the prefill attention launch
 
     # ---- context helpers -------------------------------------------------------------

@@ -31,17 +31,20 @@ class CompactorCompression(BaseCompressionMethod):
     @staticmethod
     def post_rope_scoring(q, k, v, pre_rope_scores, context) -> Optional[torch.Tensor]:
         cc = context.compression_context
-        # The reference launches this on the main stream while pre_rope_scores is
-        # still being produced on STORE_STREAM without a wait (compactor.py:44-59,
-        # SURVEY 7.3-7).  Here the consumer waits on the producer stream.
-        if context.STORE_STREAM is not None and pre_rope_scores is not None:
-            torch.cuda.current_stream().wait_stream(context.STORE_STREAM)
-        return non_causal_attn_scores(
+        # The reference launches this on the main stream while pre_rope_scores is still being
+        # produced on STORE_STREAM without a wait (compactor.py:44-59).  Here the
+        # whole scoring chain stays on STORE_STREAM: it is ordered after the leverage kernels by
+        # the stream itself, its only consumer (extract_and_store_top_kv in Attention.forward)
+        # runs on the same stream, and the attention kernel on the main stream starts without
+        # waiting for any of it — scoring, selection and compaction all overlap attention.
+        return maybe_execute_in_stream(
+            non_causal_attn_scores,
             q, k, v, context.cu_seqlens_q, context.max_seqlen_q,
             chunk_size=CompactorCompression.chunk_size, sm_scale=1.0, normalize=True,
             accum_scores=pre_rope_scores, context_lens=cc.context_lens,
             protected_first_tokens=cc.protected_first_tokens,
             protected_last_tokens=cc.protected_last_tokens, accum_blending=0.5,
+            STORE_STREAM=context.STORE_STREAM,
         )
 
 

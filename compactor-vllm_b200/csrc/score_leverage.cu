@@ -8,7 +8,7 @@
 //   X   = round16(K_h . PHI)                mma.sync, K rows straight from global
 //   Xc  = round16(X - round16(mean_t X))    per chunk
 //   G   = fp32(round16(Xc^T Xc)) + reg*I    mma.sync on the transposed sketch
-//   G   = V diag(lam) V^T                   parallel cyclic Jacobi, fp32, in smem
+//   G   = V diag(lam) V^T                   Householder + implicit QL, fp32, one warp per matrix
 //   u   = round16(Xc . round16(V |lam|^-1/2));  score = round16(sum_j round16(u_j^2))
 //
 // The reference keeps X, Xc, G, V S^-1/2, U and the row sums in K's 16-bit
@@ -18,6 +18,8 @@
 // here — an exact fp32 x^T G^-1 x only overlaps ~80 % with the reference's
 // kept set (tests/test_oracle_golden.py).  Work is ~170 KFLOP/token: latency
 // and launch count, not throughput, is what the fusion removes.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "mma.cuh"
 
@@ -27,8 +29,6 @@ constexpr int kLevThreads = 256;
 constexpr int kSk = 48;            // sketch columns
 constexpr int kTokTile = 256;      // tokens per smem tile
 constexpr int kXtStride = kTokTile + 8;  // 16-bit elements per sketch row (pad: bank spread)
-constexpr int kJacobiSweeps = 8;     // upper bound (8 == 10 in score accuracy, tools/leverage_sweeps.py); sweeps stop once no rotation moves G any more
-constexpr int kEigThreads = 128;
 
 struct LevParams {
   const void* k;
@@ -210,147 +210,204 @@ __global__ void __launch_bounds__(kLevThreads, 2) leverage_gram_kernel(const Lev
   if (tid < kSk) p.mean[(int64_t)(ch * p.HKV + h) * kSk + tid] = sm.mean[tid];
 }
 
-// ---- kernel 2: grid (n_chunks * HKV): symmetric eigendecomposition, parallel cyclic Jacobi ----
-// 24 disjoint (p,q) pairs per round, 47 rounds per sweep (round-robin tournament).  A round is
-//   phase 1  24 threads: rotation (c,s) of each pair from the current G
-//   phase 2  all threads: G <- J^T G J as 24x24 independent 2x2 blocks, V <- V J
-// in place (every element belongs to exactly one block), two barriers per round.
-// out: sv[(ch*HKV+h)][48][48] = round16(V |lam|^-1/2)   (compactor.py:197: S of a symmetric G is |lam|)
-struct EigSmem {
-  float g[kSk][kSk + 1];
-  float v[kSk][kSk + 1];
-  float4 rot[kSk / 2];  // (c, s, p, q) of each pair; p, q as int bit patterns
-  int any_rot;
+// ---- kernel 2: symmetric eigendecomposition, one WARP per matrix — Householder tridiagonalisation, accumulation of the
+// reflectors and implicit-shift QL (the EISPACK tred2 / tql2 pair, restated for a warp: lanes own
+// matrix rows, the scalar recurrences are computed redundantly by every lane).  ~1900 dependent
+// rotations of ~50 cycles each; a block-wide parallel cyclic Jacobi (the first version of this kernel)
+// moved 27 MB through shared memory per matrix, this moves 2.7 MB.
+// out: sv[(ch*HKV+h)][48][48] = round16(V |lam|^-1/2)   (compactor.py:197: S of a symmetric G is |lam|);
+// the column (eigenpair) order is arbitrary, the score sums over all of them.
+constexpr int kQlWarps = 16;  // matrices per CTA: few, fat CTAs block few SMs while attention runs beside them
+struct QlSmem {
+  float a[kSk][kSk + 1];
+  float d[kSk], e[kSk], hh[kSk], u[kSk], q[kSk];
 };
 
-__device__ __forceinline__ float rcp_approx(float x) {
-  float y;
-  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
-__device__ __forceinline__ float sqrt_approx(float x) {
-  float y;
-  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
+__device__ __forceinline__ float rsqrt_nr(float x) {  // MUFU.RSQ + one Newton step; 0 -> 0
+  if (!(x > 0.f)) return 0.f;
+  const float y = rsqrtf(x);
+  return y * fmaf(-0.5f * x * y, y, 1.5f);
 }
 
 template <bool BF16>
-__global__ void __launch_bounds__(kEigThreads, 4) leverage_eig_kernel(const float* __restrict__ gram,
-                                                                   float* __restrict__ sv_out,
-                                                                   const int32_t* __restrict__ chunk_offsets,
-                                                                   int HKV) {
-  __shared__ EigSmem sm;
-  const int ch = blockIdx.x / HKV;
+__global__ void __launch_bounds__(kQlWarps * 32) leverage_eigql_kernel(const float* __restrict__ gram,
+                                                                      float* __restrict__ sv_out,
+                                                                      const int32_t* __restrict__ chunk_offsets,
+                                                                      int HKV, int mats) {
+  extern __shared__ __align__(16) unsigned char ql_smem_raw[];
+  QlSmem* sm_all = reinterpret_cast<QlSmem*>(ql_smem_raw);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int mat = blockIdx.x * kQlWarps + warp;
+  if (mat >= mats) return;
+  const int ch = mat / HKV;
   if (chunk_offsets[ch + 1] - chunk_offsets[ch] <= 0) return;
-  const int tid = threadIdx.x;
-  const float* gin = gram + (int64_t)blockIdx.x * kSk * kSk;
-  for (int i = tid; i < kSk * kSk; i += kEigThreads) {
-    const int a = i / kSk, b = i - a * kSk;
-    sm.g[a][b] = gin[i];
-    sm.v[a][b] = (a == b) ? 1.f : 0.f;
-  }
-  if (tid == 0) sm.any_rot = 0;
-  __syncthreads();
+  QlSmem& s = sm_all[warp];
+  constexpr int n = kSk;
+  const float* gin = gram + (int64_t)mat * n * n;
+  for (int i = lane; i < n * n; i += 32) s.a[i / n][i % n] = gin[i];
+  __syncwarp();
+  const int j0 = lane, j1 = lane + 32;  // the two rows (or columns) of this lane; j1 valid for lane < 16
+  const bool has1 = j1 < n;
 
-  constexpr int NP = kSk / 2;                                      // 24 pairs
-  constexpr int GB = (NP * NP + kEigThreads - 1) / kEigThreads;    // G blocks per thread (5)
-  constexpr int VB = (NP * kSk + kEigThreads - 1) / kEigThreads;   // V items per thread (9)
-  for (int sweep = 0; sweep < kJacobiSweeps; ++sweep) {
-    for (int rnd = 0; rnd < kSk - 1; ++rnd) {
-      if (tid < NP) {
-        // round-robin tournament: position 0 fixed, the others rotate
-        const int n = kSk;
-        int a = (tid == 0) ? 0 : 1 + (tid - 1 + rnd) % (n - 1);
-        int b = 1 + (n - 2 - tid + rnd) % (n - 1);
-        if (tid == 0) b = 1 + (n - 2 + rnd) % (n - 1);
-        const int pp = min(a, b), qq = max(a, b);
-        const float app = sm.g[pp][pp], aqq = sm.g[qq][qq], apq = sm.g[pp][qq];
-        float c = 1.f, s = 0.f;
-        if (fabsf(apq) > 1e-30f) {
-          // the rotation only has to be orthogonal (c^2 + s^2 = 1 to an ulp: c = rsqrt(1 + t^2),
-          // s = t c), not the exact annihilator: approximate rcp / sqrt keep the chain short
-          const float tau = (aqq - app) * 0.5f * rcp_approx(apq);
-          const float t = copysignf(rcp_approx(fabsf(tau) + sqrt_approx(fmaf(tau, tau, 1.f))), tau);
-          c = rsqrtf(fmaf(t, t, 1.f));
-          s = t * c;
-          // still moving? (below this the rotation is the identity in fp32)
-          if (apq * apq > 1e-14f * fabsf(app * aqq)) sm.any_rot = 1;
-        }
-        sm.rot[tid] = make_float4(c, s, __int_as_float(pp), __int_as_float(qq));
-      }
-      __syncthreads();
-      {
-        // The kernel is bound by shared-memory wavefronts, so the item -> lane maps are chosen for
-        // the banks: G block (i, j) with j fastest (g[p_i][p_j] over distinct p_j: <= 2-way), V item
-        // (i, row) with row fastest (v[row][p_i], stride 49: conflict-free).  Every load is issued
-        // before the first in-place store (the stores would otherwise serialise the iterations).
-        float4 gi[GB], gj[GB];
-        float gpp[GB], gpq[GB], gqp[GB], gqq[GB];
-#pragma unroll
-        for (int u = 0; u < GB; ++u) {
-          const int it = tid + u * kEigThreads;
-          if (it < NP * NP) {
-            const int i = it / NP, j = it - i * NP;
-            gi[u] = sm.rot[i];
-            gj[u] = sm.rot[j];
-            const int pi = __float_as_int(gi[u].z), qi = __float_as_int(gi[u].w);
-            const int pj = __float_as_int(gj[u].z), qj = __float_as_int(gj[u].w);
-            gpp[u] = sm.g[pi][pj]; gpq[u] = sm.g[pi][qj];
-            gqp[u] = sm.g[qi][pj]; gqq[u] = sm.g[qi][qj];
-          }
-        }
-        float4 vi[VB];
-        float vp[VB], vq[VB];
-#pragma unroll
-        for (int u = 0; u < VB; ++u) {
-          const int it = tid + u * kEigThreads;
-          if (it < NP * kSk) {
-            const int i = it / kSk, row = it - i * kSk;
-            vi[u] = sm.rot[i];
-            vp[u] = sm.v[row][__float_as_int(vi[u].z)];
-            vq[u] = sm.v[row][__float_as_int(vi[u].w)];
-          }
-        }
-        // G blocks: rows {p_i, q_i} x cols {p_j, q_j}:  J_i^T . G . J_j
-#pragma unroll
-        for (int u = 0; u < GB; ++u) {
-          const int it = tid + u * kEigThreads;
-          if (it < NP * NP) {
-            const int pi = __float_as_int(gi[u].z), qi = __float_as_int(gi[u].w);
-            const int pj = __float_as_int(gj[u].z), qj = __float_as_int(gj[u].w);
-            const float ci = gi[u].x, si = gi[u].y, cj = gj[u].x, sj = gj[u].y;
-            const float rpp = ci * gpp[u] - si * gqp[u], rpq = ci * gpq[u] - si * gqq[u];
-            const float rqp = si * gpp[u] + ci * gqp[u], rqq = si * gpq[u] + ci * gqq[u];
-            sm.g[pi][pj] = cj * rpp - sj * rpq;
-            sm.g[pi][qj] = sj * rpp + cj * rpq;
-            sm.g[qi][pj] = cj * rqp - sj * rqq;
-            sm.g[qi][qj] = sj * rqp + cj * rqq;
-          }
-        }
-        // V <- V J_i
-#pragma unroll
-        for (int u = 0; u < VB; ++u) {
-          const int it = tid + u * kEigThreads;
-          if (it < NP * kSk) {
-            const int i = it / kSk, row = it - i * kSk;
-            const float c = vi[u].x, s = vi[u].y;
-            sm.v[row][__float_as_int(vi[u].z)] = c * vp[u] - s * vq[u];
-            sm.v[row][__float_as_int(vi[u].w)] = s * vp[u] + c * vq[u];
-          }
-        }
-      }
-      __syncthreads();
+  // ---- Householder reduction to tridiagonal form; u^(i) is parked in column i (rows < i) ----
+  for (int i = n - 1; i >= 2; --i) {
+    float x0 = (j0 < i) ? s.a[i][j0] : 0.f;
+    float x1 = (has1 && j1 < i) ? s.a[i][j1] : 0.f;
+    const float scale = warp_sum(fabsf(x0) + fabsf(x1));
+    if (scale == 0.f) {  // row already reduced: H_i = I
+      if (lane == 0) { s.e[i] = 0.f; s.hh[i] = 0.f; s.d[i] = s.a[i][i]; }
+      __syncwarp();
+      continue;
     }
-    const bool done = sm.any_rot == 0;
-    __syncthreads();
-    if (done) break;
-    if (tid == 0) sm.any_rot = 0;
+    const float inv = 1.f / scale;
+    x0 *= inv; x1 *= inv;
+    float h = warp_sum(x0 * x0 + x1 * x1);
+    const float f = (i - 1 < 32) ? __shfl_sync(0xffffffffu, x0, i - 1) : __shfl_sync(0xffffffffu, x1, i - 33);
+    const float g = -copysignf(sqrtf(h), f);
+    h -= f * g;
+    if (j0 == i - 1) x0 = f - g;
+    if (j1 == i - 1) x1 = f - g;
+    if (j0 < i) { s.u[j0] = x0; s.a[j0][i] = x0; }
+    if (has1 && j1 < i) { s.u[j1] = x1; s.a[j1][i] = x1; }
+    if (lane == 0) { s.e[i] = scale * g; s.hh[i] = h; s.d[i] = s.a[i][i]; }
+    __syncwarp();
+    // p = A u / h  (rows >= i compute garbage that is never used)
+    float p0 = 0.f, p1 = 0.f;
+    for (int k = 0; k < i; ++k) {
+      const float uk = s.u[k];
+      p0 = fmaf(s.a[j0][k], uk, p0);
+      if (has1) p1 = fmaf(s.a[j1][k], uk, p1);
+    }
+    const float rh = 1.f / h;
+    p0 *= rh; p1 *= rh;
+    const float K = warp_sum(((j0 < i) ? x0 * p0 : 0.f) + ((has1 && j1 < i) ? x1 * p1 : 0.f)) * 0.5f * rh;
+    const float q0 = p0 - K * x0, q1 = p1 - K * x1;
+    if (j0 < i) s.q[j0] = q0;
+    if (has1 && j1 < i) s.q[j1] = q1;
+    __syncwarp();
+    // A <- A - u q^T - q u^T on the leading i x i block (kept fully symmetric)
+    for (int k = 0; k < i; ++k) {
+      const float uk = s.u[k], qk = s.q[k];
+      if (j0 < i) s.a[j0][k] -= fmaf(x0, qk, q0 * uk);
+      if (has1 && j1 < i) s.a[j1][k] -= fmaf(x1, qk, q1 * uk);
+    }
     __syncwarp();
   }
-  float* out = sv_out + (int64_t)blockIdx.x * kSk * kSk;
-  for (int i = tid; i < kSk * kSk; i += kEigThreads) {
-    const int a = i / kSk, b = i - a * kSk;
-    out[i] = round16<BF16>(sm.v[a][b] * rsqrtf(fabsf(sm.g[b][b])));
+  if (lane == 0) {
+    s.d[0] = s.a[0][0]; s.d[1] = s.a[1][1];
+    s.e[1] = s.a[1][0]; s.e[0] = 0.f;
+    s.a[0][0] = 1.f;
+  }
+  __syncwarp();
+
+  // ---- Z = H_{n-1} ... H_2, built in place: lanes own columns ----
+  for (int i = 2; i <= n; ++i) {
+    // row / column i-1 of the growing block become the identity (column i-1 held u^(i-1), consumed)
+    if (j0 < i - 1) { s.a[i - 1][j0] = 0.f; s.a[j0][i - 1] = 0.f; }
+    if (has1 && j1 < i - 1) { s.a[i - 1][j1] = 0.f; s.a[j1][i - 1] = 0.f; }
+    if (lane == 0) s.a[i - 1][i - 1] = 1.f;
+    __syncwarp();
+    if (i < n) {
+      const float h = s.hh[i];
+      if (h != 0.f) {
+        float g0 = 0.f, g1 = 0.f;
+        for (int k = 0; k < i; ++k) {
+          const float uk = s.a[k][i];
+          g0 = fmaf(uk, s.a[k][j0], g0);
+          if (has1) g1 = fmaf(uk, s.a[k][j1], g1);
+        }
+        const float rh = 1.f / h;
+        g0 *= rh; g1 *= rh;
+        for (int k = 0; k < i; ++k) {
+          const float uk = s.a[k][i];
+          if (j0 < i) s.a[k][j0] = fmaf(-g0, uk, s.a[k][j0]);
+          if (has1 && j1 < i) s.a[k][j1] = fmaf(-g1, uk, s.a[k][j1]);
+        }
+      }
+      __syncwarp();
+    }
+  }
+
+  // ---- implicit-shift QL on (d, e); rotations accumulated into Z (lanes own rows) ----
+  {
+    const float e0 = s.e[j0 + 1 < n ? j0 + 1 : 0];
+    const float e1 = (has1 && j1 + 1 < n) ? s.e[j1 + 1] : 0.f;
+    __syncwarp();
+    s.e[j0] = e0;  // j0 + 1 < n always holds for j0 <= 31
+    if (has1) s.e[j1] = e1;
+    __syncwarp();
+  }
+  float fsh = 0.f, tst1 = 0.f;
+  const float eps = 1.1920929e-7f;
+  for (int l = 0; l < n; ++l) {
+    tst1 = fmaxf(tst1, fabsf(s.d[l]) + fabsf(s.e[l]));
+    int m = l;
+    while (m < n && fabsf(s.e[m]) > eps * tst1) ++m;  // e[n-1] == 0 ends the scan
+    if (m > l) {
+      int iter = 0;
+      float el_abs;
+      do {
+        ++iter;
+        const float g0 = s.d[l], el = s.e[l], el1 = s.e[l + 1];
+        float pp = (s.d[l + 1] - g0) / (2.f * el);
+        float rr = sqrtf(fmaf(pp, pp, 1.f));
+        if (pp < 0.f) rr = -rr;
+        const float dl = el / (pp + rr), dl1 = el * (pp + rr);
+        const float hs = g0 - dl;
+        const float dj0 = s.d[j0], dj1 = has1 ? s.d[j1] : 0.f;
+        float pcur = s.d[m];
+        __syncwarp();
+        if (j0 >= l + 2) s.d[j0] = dj0 - hs;
+        if (has1 && j1 >= l + 2) s.d[j1] = dj1 - hs;
+        if (lane == 0) { s.d[l] = dl; s.d[l + 1] = dl1; }
+        __syncwarp();
+        if (m >= l + 2 && m < n) pcur = s.d[m];  // d[m] was shifted by hs above
+        else if (m == l + 1) pcur = dl1;
+        fsh += hs;
+        float c = 1.f, c2 = 1.f, c3 = 1.f, sn = 0.f, s2 = 0.f;
+        // column m of Z is carried in registers from one rotation to the next
+        float z0 = s.a[j0][m], z1 = has1 ? s.a[j1][m] : 0.f;
+        float ei = s.e[m - 1], di = s.d[m - 1];
+        for (int i = m - 1; i >= l; --i) {
+          const float ein = (i > l) ? s.e[i - 1] : 0.f, din = (i > l) ? s.d[i - 1] : 0.f;  // prefetch
+          c3 = c2; c2 = c; s2 = sn;
+          const float g = c * ei, h = c * pcur;
+          const float x2 = fmaf(pcur, pcur, ei * ei);
+          const float ri = rsqrt_nr(x2);
+          const float r = x2 * ri;
+          sn = ei * ri;
+          c = pcur * ri;
+          pcur = c * di - sn * g;
+          if (lane == 0) { s.e[i + 1] = s2 * r; s.d[i + 1] = h + sn * (c * g + sn * di); }
+          // Z[:, i+1] = sn Z[:, i] + c Z[:, i+1];  Z[:, i] = c Z[:, i] - sn Z[:, i+1]
+          const float y0 = s.a[j0][i];
+          s.a[j0][i + 1] = fmaf(sn, y0, c * z0);
+          z0 = fmaf(c, y0, -sn * z0);
+          if (has1) {
+            const float y1 = s.a[j1][i];
+            s.a[j1][i + 1] = fmaf(sn, y1, c * z1);
+            z1 = fmaf(c, y1, -sn * z1);
+          }
+          ei = ein; di = din;
+        }
+        s.a[j0][l] = z0;
+        if (has1) s.a[j1][l] = z1;
+        const float pe = -sn * s2 * c3 * el1 * s.e[l] / dl1;
+        el_abs = fabsf(sn * pe);
+        __syncwarp();
+        if (lane == 0) { s.e[l] = sn * pe; s.d[l] = c * pe; }
+        __syncwarp();
+      } while (el_abs > eps * tst1 && iter < 60);
+    }
+    __syncwarp();
+    if (lane == 0) { s.d[l] += fsh; s.e[l] = 0.f; }
+    __syncwarp();
+  }
+
+  float* out = sv_out + (int64_t)mat * n * n;
+  for (int i = lane; i < n * n; i += 32) {
+    const int a = i / n, b = i - a * n;
+    out[i] = round16<BF16>(s.a[a][b] * rsqrtf(fabsf(s.d[b])));
   }
 }
 
@@ -489,17 +546,19 @@ extern "C" int cvllm_leverage_scores(const void* k_pre, int64_t k_stride_n, int6
     CVLLM_CHECK_CUDA(cudaFuncSetAttribute(leverage_gram_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     CVLLM_CHECK_CUDA(cudaFuncSetAttribute(leverage_score_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     CVLLM_CHECK_CUDA(cudaFuncSetAttribute(leverage_score_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CVLLM_CHECK_CUDA(cudaFuncSetAttribute(leverage_eigql_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(QlSmem) * kQlWarps)));
+    CVLLM_CHECK_CUDA(cudaFuncSetAttribute(leverage_eigql_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(QlSmem) * kQlWarps)));
     attr_set = true;
   }
   const dim3 grid(n_chunks, HKV);
   if (dtype == CVLLM_BF16) {
     leverage_gram_kernel<true><<<grid, kLevThreads, smem, st>>>(p);
-    leverage_eig_kernel<true><<<(unsigned)mats, kEigThreads, 0, st>>>(p.gram, p.sv, chunk_offsets, HKV);
+    leverage_eigql_kernel<true><<<(unsigned)((mats + kQlWarps - 1) / kQlWarps), kQlWarps * 32, sizeof(QlSmem) * kQlWarps, st>>>(p.gram, p.sv, chunk_offsets, HKV, (int)mats);
     leverage_score_kernel<true><<<grid, kLevThreads, smem, st>>>(p);
     leverage_finalize_kernel<true><<<n_chunks, 256, 0, st>>>(p.raw, chunk_offsets, out_scores, HKV, normalize);
   } else {
     leverage_gram_kernel<false><<<grid, kLevThreads, smem, st>>>(p);
-    leverage_eig_kernel<false><<<(unsigned)mats, kEigThreads, 0, st>>>(p.gram, p.sv, chunk_offsets, HKV);
+    leverage_eigql_kernel<false><<<(unsigned)((mats + kQlWarps - 1) / kQlWarps), kQlWarps * 32, sizeof(QlSmem) * kQlWarps, st>>>(p.gram, p.sv, chunk_offsets, HKV, (int)mats);
     leverage_score_kernel<false><<<grid, kLevThreads, smem, st>>>(p);
     leverage_finalize_kernel<false><<<n_chunks, 256, 0, st>>>(p.raw, chunk_offsets, out_scores, HKV, normalize);
   }
