@@ -289,8 +289,7 @@ def decode_bench(device, dtype, B: int, lens_bh: torch.Tensor, iters: int, flush
     """One decode step = decode_store_kv + head_sparse_decode_attention on a synthetic compacted cache,
     captured in a CUDA graph and replayed (how the reference engine runs decode, core/model_runner.py:524-528);
     every replay is timed with CUDA events after a cold-L2 flush.  Returns (ms per step, algorithmic bytes)."""
-    from compactor_vllm.attention.sparse_decode_kernel import head_sparse_decode_attention
-    from compactor_vllm.kv_cache.store_kv_cache import decode_store_kv
+    from compactor_vllm.attention.sparse_decode_kernel import decode_append_and_attend
     g = torch.Generator().manual_seed(seed)
     warm = 8
     nlp = int((int(lens_bh.max()) + iters + warm + 8 + PS - 1) // PS)
@@ -299,15 +298,14 @@ def decode_bench(device, dtype, B: int, lens_bh: torch.Tensor, iters: int, flush
     kc = torch.randn((n_pages * PS, D), device=device, dtype=dtype)
     vc = torch.randn((n_pages * PS, D), device=device, dtype=dtype)
     bm = torch.arange(1, B + 1, dtype=torch.int32, device=device)
-    lens = lens_bh.to(torch.int32).to(device).contiguous()
+    lens = torch.zeros((B + 1, HKV), dtype=torch.int32, device=device)  # the cache's bh_seq_lens table, slot 0 reserved
+    lens[1:] = lens_bh.to(torch.int32).to(device)
     q = torch.randn((B, HQ, D), device=device, dtype=dtype)
     kn = torch.randn((B, HKV, D), device=device, dtype=dtype)
     vn = torch.randn((B, HKV, D), device=device, dtype=dtype)
 
-    def step():
-        decode_store_kv(key=kn, value=vn, batch_mapping=bm, bh_lens=lens, page_table=pt, k_cache=kc,
-                        v_cache=vc, PAGE_SIZE=PS)
-        return head_sparse_decode_attention(q, kc, vc, lens, pt, bm, HKV, PS)
+    def step():  # what Attention.forward's decode branch launches: append kernel + attention kernel
+        return decode_append_and_attend(q, kn, vn, kc, vc, lens, pt, bm, HKV, PS)
 
     gs = torch.cuda.Stream(device=device)
     gs.wait_stream(torch.cuda.current_stream())

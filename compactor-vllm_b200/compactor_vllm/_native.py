@@ -39,6 +39,8 @@ _SIGNATURES = {
     "cvllm_decode_attention_workspace_bytes": (_sz, [_i, _i, _i, _i, _i]),
     "cvllm_decode_attention": (_i, [_p, _p, _p, _p, _p, _p, _p, _p, _sz, _i, _i, _i, _i, _i, _i,
                                     _f, _i, _i, _p]),
+    "cvllm_decode_step": (_i, [_p, _p, _i64, _i64, _i64, _i64, _p, _p, _p, _p, _p, _p, _p, _p, _sz,
+                               _i, _i, _i, _i, _i, _i, _f, _i, _i, _i, _p]),
     "cvllm_prefill_attention": (_i, [_p, _p, _p, _p, _p, _p, _p, _p, _p, _p,
                                      _i, _i, _i, _i, _i, _i, _i, _i64, _i64, _i64, _i64, _i64, _i,
                                      _f, _i, _p]),

@@ -69,6 +69,53 @@ def head_sparse_decode_attention(
     return out
 
 
+def decode_append_and_attend(
+    q: torch.Tensor,  # [B, HQ, D]
+    key: torch.Tensor,  # [B, HKV, D] new row per (b, h)
+    value: torch.Tensor,
+    k_cache: torch.Tensor,
+    v_cache: torch.Tensor,
+    bh_seq_lens: torch.Tensor,  # the cache's [Bmax+1, HKV] table, updated in place (+1 per live (b, h))
+    global_page_table: torch.Tensor,
+    batch_mapping: torch.Tensor,
+    HKV: int,
+    PAGE_SIZE: int,
+    sm_scale: float = None,
+    reserved_batch: int = 0,
+):
+    """The decode branch of layers/attention.py:133-160 as one native call (cvllm_decode_step):
+    decode_store_kv + head_sparse_decode_attention, both reading / bumping `bh_seq_lens` through
+    `batch_mapping` — no gathered length copy, no index_copy_ back.  Graph-capturable, two kernel nodes."""
+    if q.ndim == 4:
+        assert q.shape[2] == 1
+        q = q.squeeze(-2)
+    B, HQ, D = q.shape
+    assert key.shape == value.shape == (B, HKV, D)
+    assert key.stride(-1) == 1 and value.stride(-1) == 1 and q.is_contiguous()
+    assert k_cache.is_contiguous() and v_cache.is_contiguous() and k_cache.dtype == q.dtype == key.dtype
+    assert bh_seq_lens.dtype == torch.int32 and bh_seq_lens.is_contiguous() and bh_seq_lens.shape[-1] == HKV
+    assert global_page_table.dtype == torch.int32 and global_page_table.is_contiguous()
+    assert batch_mapping.dtype == torch.int32 and batch_mapping.is_contiguous()
+    assert HQ % HKV == 0 and PAGE_SIZE % 32 == 0
+    sm_scale = 1 / math.sqrt(D) if sm_scale is None else sm_scale
+    dev = q.device
+    out = torch.empty_like(q)
+    if B == 0:
+        return out
+    L = N.lib()
+    ws_bytes = L.cvllm_decode_attention_workspace_bytes(B, HQ, HKV, D, 0)
+    ws = N.workspace(dev, ws_bytes, f"decode_attn:{B}:{HQ}:{HKV}", zero=True)
+    rc = L.cvllm_decode_step(
+        N.ptr(key), N.ptr(value), key.stride(0), key.stride(1), value.stride(0), value.stride(1),
+        N.ptr(q), N.ptr(out), N.ptr(k_cache), N.ptr(v_cache), N.ptr(bh_seq_lens), N.ptr(global_page_table),
+        N.ptr(batch_mapping), N.ptr(ws), ws.numel(), B, HQ, HKV, D, int(PAGE_SIZE),
+        global_page_table.shape[-1], float(sm_scale), N.dtype_code(q.dtype), int(reserved_batch), 0,
+        N.stream(dev),
+    )
+    N.check(rc, "cvllm_decode_step")
+    return out
+
+
 @functools.lru_cache(maxsize=128)
 def num_splits_heuristic(total_mblocks: int, max_seq_len: int, num_sms: int, max_splits: int) -> int:
     """Split count the reference engine fixes at graph-capture time (:168-192).

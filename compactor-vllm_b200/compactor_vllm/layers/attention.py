@@ -9,9 +9,10 @@ v_cache, page_table, bh_seq_lens and page_size (core/memory_manager.py).
 from typing import Optional
 
 import torch
-from compactor_vllm.attention.sparse_decode_kernel import head_sparse_decode_attention
+from compactor_vllm.attention.sparse_decode_kernel import decode_append_and_attend, head_sparse_decode_attention
 from compactor_vllm.attention.sparse_varlen_kernel import causal_sparse_varlen_with_cache
 from compactor_vllm.compression.common import extract_and_store_top_kv
+from compactor_vllm.config.constants import RESERVED_BATCH
 from compactor_vllm.config.engine_config import AttentionBackend
 from compactor_vllm.kv_cache.store_kv_cache import decode_store_kv, prefill_store_all_kv
 from compactor_vllm.utils.context import Context, get_context
@@ -35,6 +36,14 @@ class Attention(nn.Module):
     def forward(self, q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, scores: Optional[torch.Tensor] = None):
         context: Context = get_context()
         batch_mapping = context.batch_mapping
+        if not context.is_prefill and self.bh_seq_lens is not None and self.bh_seq_lens.is_contiguous():
+            # decode: append + attend index bh_seq_lens through batch_mapping themselves — the
+            # reference's index_select / index_copy_ round trip (:46-50,152-160) is not needed
+            assert self.k_cache is not None, "KV Cache must be initialized for decoding"
+            return decode_append_and_attend(
+                q, k, v, self.k_cache, self.v_cache, self.bh_seq_lens, self.page_table, batch_mapping,
+                int(self.num_kv_heads), self.page_size, self.scale, reserved_batch=RESERVED_BATCH,
+            )
         seq_lens = (
             None if self.bh_seq_lens is None
             else self.bh_seq_lens.index_select(0, batch_mapping).contiguous()

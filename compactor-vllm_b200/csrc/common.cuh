@@ -63,6 +63,11 @@ void note_launches(int n);
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 int sm_count();
+int launch_decode_store(const void* key, const void* value, int64_t sk_b, int64_t sk_h, int64_t sv_b,
+                        int64_t sv_h, const int32_t* batch_mapping, int32_t* bh_lens,
+                        const int32_t* page_table, void* k_cache, void* v_cache, int B, int HKV, int D,
+                        int PS, int NLP, int elem_bytes, int reserved_batch, int lens_by_slot,
+                        cvllm_stream_t stream);
 uint64_t launches();
 
 // ---------------------------------------------------------------------------

@@ -51,6 +51,7 @@ struct DecodeParams {
   int B, HQ, HKV, G, PS, NLP;
   int box_rows;       // min(PS, 128): rows of one TMA box (a box never crosses a page)
   int slots;          // ring depth (<= kMaxSlots)
+  int lens_by_slot;   // seq_lens_bh is the cache's [Bmax+1, HKV] table, indexed through batch_mapping
   int mode;           // 0 = normal; 1 = consumers only drain the ring (load ceiling, profiling only)
   float scale_log2;
 };
@@ -108,6 +109,12 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_consta
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int C = gridDim.x, c = blockIdx.x;
   const int G = p.G;
+  // rows cached for flattened head i = b * HKV + h
+  auto len_of = [&](int i) -> int {
+    if (!p.lens_by_slot) return p.seq_lens_bh[i];
+    const int b = i / p.HKV;
+    return p.seq_lens_bh[p.batch_mapping[b] * p.HKV + (i - b * p.HKV)];
+  };
 
   if (tid == kDecCons) {  // producer warp: descriptor fetch overlaps the prologue
     tma_prefetch_desc(&tm_k);
@@ -126,7 +133,7 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_consta
     const int per = cdiv(BH, kDecThreads);
     const int beg = min(BH, tid * per), end = min(BH, beg + per);
     int local = 0;
-    for (int i = beg; i < end; ++i) local += cdiv(p.seq_lens_bh[i], kUnit);
+    for (int i = beg; i < end; ++i) local += cdiv(len_of(i), kUnit);
     int incl = local;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -140,7 +147,7 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_consta
     int run = base + incl - local;
     for (int i = beg; i < end; ++i) {
       s_prefix[i] = run;
-      run += cdiv(p.seq_lens_bh[i], kUnit);
+      run += cdiv(len_of(i), kUnit);
     }
     if (tid == kDecThreads - 1) s_prefix[BH] = run;
     __syncthreads();
@@ -186,7 +193,7 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_consta
       if (my_unit < u_end) {
         const int head = find_head(my_unit);
         const int t0 = (my_unit - s_prefix[head]) * kUnit;
-        const int L = p.seq_lens_bh[head];
+        const int L = len_of(head);
         nvp = min(pieces, cdiv(L - t0, BR));  // pages past the head's length are not mapped
         if (my_piece < nvp) {
           const int b = head / p.HKV, h = head % p.HKV;
@@ -245,7 +252,7 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_consta
     const int seg_end = min(u_end, h_end);
     const int ua = u - h_beg, ub = seg_end - h_beg;  // units of this head
     const int b = head / p.HKV, h = head % p.HKV;
-    const int L = p.seq_lens_bh[head];
+    const int L = len_of(head);
 
     // ---- Q^T as B operand (n = query r, k = permuted d) ----
     uint32_t qb[KSTEPS][2];
@@ -515,12 +522,11 @@ extern "C" size_t cvllm_decode_attention_workspace_bytes(int B, int HQ, int HKV,
   return decode_counter_bytes(BH) + slots * G * (D + 2) * sizeof(float);
 }
 
-extern "C" int cvllm_decode_attention(const void* q, void* out, const void* k_cache,
-                                      const void* v_cache, const int32_t* seq_lens_bh,
-                                      const int32_t* page_table, const int32_t* batch_mapping,
-                                      void* workspace, size_t workspace_bytes, int B, int HQ, int HKV,
-                                      int D, int PS, int NLP, float sm_scale, int dtype, int num_ctas,
-                                      cvllm_stream_t stream) {
+static int launch_decode_attn(const void* q, void* out, const void* k_cache, const void* v_cache,
+                              const int32_t* seq_lens_bh, const int32_t* page_table,
+                              const int32_t* batch_mapping, void* workspace, size_t workspace_bytes, int B,
+                              int HQ, int HKV, int D, int PS, int NLP, float sm_scale, int dtype,
+                              int num_ctas, int lens_by_slot, cvllm_stream_t stream) {
   CVLLM_CHECK_ARG(B >= 0 && HQ > 0 && HKV > 0 && PS > 0 && NLP > 0);
   if (B == 0) return CVLLM_OK;
   CVLLM_CHECK_ARG(q && out && k_cache && v_cache && seq_lens_bh && page_table && batch_mapping &&
@@ -547,6 +553,7 @@ extern "C" int cvllm_decode_attention(const void* q, void* out, const void* k_ca
   p.scratch = reinterpret_cast<float*>(reinterpret_cast<char*>(workspace) + counters_bytes);
   p.B = B; p.HQ = HQ; p.HKV = HKV; p.G = G; p.PS = PS; p.NLP = NLP;
   p.box_rows = PS < kUnit ? PS : kUnit;
+  p.lens_by_slot = lens_by_slot;
   p.scale_log2 = sm_scale * 1.4426950408889634f;
   {
     static const int mode = [] { const char* e = getenv("CVLLM_DECODE_MODE"); return e ? atoi(e) : 0; }();
@@ -595,4 +602,30 @@ extern "C" int cvllm_decode_attention(const void* q, void* out, const void* k_ca
   }
   CVLLM_CHECK_LAUNCH();
   return CVLLM_OK;
+}
+
+extern "C" int cvllm_decode_attention(const void* q, void* out, const void* k_cache,
+                                      const void* v_cache, const int32_t* seq_lens_bh,
+                                      const int32_t* page_table, const int32_t* batch_mapping,
+                                      void* workspace, size_t workspace_bytes, int B, int HQ, int HKV,
+                                      int D, int PS, int NLP, float sm_scale, int dtype, int num_ctas,
+                                      cvllm_stream_t stream) {
+  return launch_decode_attn(q, out, k_cache, v_cache, seq_lens_bh, page_table, batch_mapping, workspace,
+                            workspace_bytes, B, HQ, HKV, D, PS, NLP, sm_scale, dtype, num_ctas, 0, stream);
+}
+
+// One decode step of Attention.forward (layers/attention.py:133-160): append the new (b, h) rows, then attend,
+// both indexing the cache's own bh_seq_lens table [Bmax+1, HKV] through batch_mapping — the reference's
+// index_select / clone / index_copy_ of a gathered length copy around the two kernels disappear.
+extern "C" int cvllm_decode_step(const void* key, const void* value, int64_t sk_b, int64_t sk_h,
+                                 int64_t sv_b, int64_t sv_h, const void* q, void* out, void* k_cache,
+                                 void* v_cache, int32_t* bh_seq_lens, const int32_t* page_table,
+                                 const int32_t* batch_mapping, void* workspace, size_t workspace_bytes,
+                                 int B, int HQ, int HKV, int D, int PS, int NLP, float sm_scale, int dtype,
+                                 int reserved_batch, int num_ctas, cvllm_stream_t stream) {
+  int rc = launch_decode_store(key, value, sk_b, sk_h, sv_b, sv_h, batch_mapping, bh_seq_lens, page_table,
+                               k_cache, v_cache, B, HKV, D, PS, NLP, 2, reserved_batch, 1, stream);
+  if (rc) return rc;
+  return launch_decode_attn(q, out, k_cache, v_cache, bh_seq_lens, page_table, batch_mapping, workspace,
+                            workspace_bytes, B, HQ, HKV, D, PS, NLP, sm_scale, dtype, num_ctas, 1, stream);
 }

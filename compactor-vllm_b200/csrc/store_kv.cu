@@ -19,7 +19,7 @@ __global__ void decode_store_kernel(const uint4* __restrict__ key, const uint4* 
                                     int32_t* __restrict__ bh_lens,
                                     const int32_t* __restrict__ page_table, uint4* __restrict__ k_cache,
                                     uint4* __restrict__ v_cache, int B, int HKV, int PS, int NLP,
-                                    int reserved_batch) {
+                                    int reserved_batch, int lens_by_slot) {
   // strides here are already in uint4 units
   const int rows = B * HKV;
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
@@ -29,7 +29,9 @@ __global__ void decode_store_kernel(const uint4* __restrict__ key, const uint4* 
   const int b = row / HKV, h = row % HKV;
   const int mapped = batch_mapping[b];
   if (mapped == reserved_batch) return;
-  const int len = bh_lens[row];
+  // lens_by_slot: bh_lens is the cache's [Bmax+1, HKV] table (no gathered copy to scatter back)
+  const int li = lens_by_slot ? mapped * HKV + h : row;
+  const int len = bh_lens[li];
   const int lp = len / PS, off = len - lp * PS;
   const int64_t phys = page_table[((int64_t)mapped * HKV + h) * NLP + lp];
   const int64_t dst = (phys * PS + off) * VEC_PER_ROW + vec;
@@ -38,7 +40,7 @@ __global__ void decode_store_kernel(const uint4* __restrict__ key, const uint4* 
   // every lane of the row group has read `len` before any of them writes it:
   // the group lives inside one warp (VEC_PER_ROW <= 32).
   __syncwarp();
-  if (vec == 0) bh_lens[row] = len + 1;
+  if (vec == 0) bh_lens[li] = len + 1;
 }
 
 // ---------------------------------------------------------------------------
@@ -135,11 +137,12 @@ __global__ void scatter_pages_kernel(const int32_t* __restrict__ add_pages,
 
 using namespace cvllm;
 
-extern "C" int cvllm_decode_store_kv(const void* key, const void* value, int64_t sk_b, int64_t sk_h,
-                                     int64_t sv_b, int64_t sv_h, const int32_t* batch_mapping,
-                                     int32_t* bh_lens, const int32_t* page_table, void* k_cache,
-                                     void* v_cache, int B, int HKV, int D, int PS, int NLP,
-                                     int elem_bytes, int reserved_batch, cvllm_stream_t stream) {
+namespace cvllm {
+int launch_decode_store(const void* key, const void* value, int64_t sk_b, int64_t sk_h, int64_t sv_b,
+                        int64_t sv_h, const int32_t* batch_mapping, int32_t* bh_lens,
+                        const int32_t* page_table, void* k_cache, void* v_cache, int B, int HKV, int D,
+                        int PS, int NLP, int elem_bytes, int reserved_batch, int lens_by_slot,
+                        cvllm_stream_t stream) {
   CVLLM_CHECK_ARG(key && value && batch_mapping && bh_lens && page_table && k_cache && v_cache);
   CVLLM_CHECK_ARG(B >= 0 && HKV > 0 && D > 0 && PS > 0 && NLP > 0);
   CVLLM_CHECK_ARG(elem_bytes == 1 || elem_bytes == 2 || elem_bytes == 4);
@@ -159,7 +162,7 @@ extern "C" int cvllm_decode_store_kv(const void* key, const void* value, int64_t
   decode_store_kernel<V><<<grid, threads, 0, st>>>(                                                \
       (const uint4*)key, (const uint4*)value, sk_b / per16, sk_h / per16, sv_b / per16,            \
       sv_h / per16, batch_mapping, bh_lens, page_table, (uint4*)k_cache, (uint4*)v_cache, B, HKV,  \
-      PS, NLP, reserved_batch)
+      PS, NLP, reserved_batch, lens_by_slot)
   switch (vpr) {
     case 1: LAUNCH(1); break;
     case 2: LAUNCH(2); break;
@@ -172,6 +175,16 @@ extern "C" int cvllm_decode_store_kv(const void* key, const void* value, int64_t
 #undef LAUNCH
   CVLLM_CHECK_LAUNCH();
   return CVLLM_OK;
+}
+}  // namespace cvllm
+
+extern "C" int cvllm_decode_store_kv(const void* key, const void* value, int64_t sk_b, int64_t sk_h,
+                                     int64_t sv_b, int64_t sv_h, const int32_t* batch_mapping,
+                                     int32_t* bh_lens, const int32_t* page_table, void* k_cache,
+                                     void* v_cache, int B, int HKV, int D, int PS, int NLP,
+                                     int elem_bytes, int reserved_batch, cvllm_stream_t stream) {
+  return cvllm::launch_decode_store(key, value, sk_b, sk_h, sv_b, sv_h, batch_mapping, bh_lens, page_table,
+                                    k_cache, v_cache, B, HKV, D, PS, NLP, elem_bytes, reserved_batch, 0, stream);
 }
 
 extern "C" int cvllm_prefill_store_all(const void* keys, const void* vals, int64_t sk_n, int64_t sk_h,

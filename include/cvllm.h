@@ -161,6 +161,18 @@ int cvllm_decode_attention(const void* q, void* out, const void* k_cache, const 
                            int PS, int NLP, float sm_scale, int dtype, int num_ctas,
                            cvllm_stream_t stream);
 
+/* The decode branch of Attention.forward (layers/attention.py:133-160) as one call: decode_store_kv followed by
+ * head_sparse_decode_attention, both indexing the cache's own `bh_seq_lens` table [Bmax+1, HKV] through
+ * `batch_mapping` (rows mapped to `reserved_batch` are skipped by the store and read length 0).  Replaces the
+ * reference's index_select / clone / index_copy_ of a gathered length copy: two kernel nodes per layer-step.
+ * 16-bit caches only; workspace contract as for cvllm_decode_attention. */
+int cvllm_decode_step(const void* key, const void* value, int64_t sk_b, int64_t sk_h,
+                      int64_t sv_b, int64_t sv_h, const void* q, void* out, void* k_cache,
+                      void* v_cache, int32_t* bh_seq_lens, const int32_t* page_table,
+                      const int32_t* batch_mapping, void* workspace, size_t workspace_bytes,
+                      int B, int HQ, int HKV, int D, int PS, int NLP, float sm_scale, int dtype,
+                      int reserved_batch, int num_ctas, cvllm_stream_t stream);
+
 /* causal_sparse_varlen_with_cache — attention/sparse_varlen_kernel.py:11-197
  * (K1 :265-519).  Causal attention of the packed new tokens over
  * [cached prefix of (b,h) || new K/V of b]; tcgen05/TMEM/TMA kernel. */

@@ -109,3 +109,41 @@ def test_decode_cuda_graph_capturable():
     graph.replay()
     torch.cuda.synchronize()
     assert torch.equal(out, eager)
+
+
+def test_decode_step_matches_store_then_attend_with_reserved_rows():
+    """cvllm_decode_step (slot-indexed lengths, what Attention.forward's decode branch calls) against the
+    reference-shaped sequence index_select -> decode_store_kv -> attention -> index_copy_, bit for bit;
+    rows mapped to RESERVED_BATCH (CUDA-graph padding, core/model_runner.py:484) are skipped."""
+    from compactor_vllm.attention.sparse_decode_kernel import decode_append_and_attend
+    from compactor_vllm.kv_cache.store_kv_cache import decode_store_kv
+    dtype, B, HQ, HKV, D, PS = torch.bfloat16, 6, 32, 8, 128, 128
+    g = torch.Generator().manual_seed(4)
+    lens = torch.randint(0, 1500, (B, HKV), generator=g)
+    lens[2, 3] = 0
+    kc, vc, pt, bm = make_paged(B, HKV, D, PS, (lens + 2).tolist(), dtype, DEV, seed=21, n_extra_slots=3)
+    bm = bm.clone()
+    bm[1] = 0
+    bm[4] = 0  # two padding rows
+    n_slots = pt.shape[0]
+    table = torch.zeros((n_slots, HKV), dtype=torch.int32, device=DEV)
+    table[bm.long()] = lens.to(torch.int32).to(DEV)
+    table[0] = 0
+    q = torch.randn((B, HQ, D), generator=g).to(dtype).to(DEV)
+    kn = torch.randn((B, HKV, D), generator=g).to(dtype).to(DEV)
+    vn = torch.randn((B, HKV, D), generator=g).to(dtype).to(DEV)
+
+    kc2, vc2, table2 = kc.clone(), vc.clone(), table.clone()
+    gathered = table2.index_select(0, bm.long()).contiguous()
+    decode_store_kv(key=kn, value=vn, batch_mapping=bm, bh_lens=gathered, page_table=pt, k_cache=kc2,
+                    v_cache=vc2, PAGE_SIZE=PS)
+    ref = head_sparse_decode_attention(q, kc2, vc2, gathered, pt, bm, HKV, PS)
+    live = bm != 0
+    table2[bm[live].long()] = gathered[live]
+
+    out = decode_append_and_attend(q, kn, vn, kc, vc, table, pt, bm, HKV, PS)
+    torch.cuda.synchronize()
+    assert torch.equal(table, table2) and (table[0] == 0).all()
+    assert torch.equal(kc.view(torch.int16), kc2.view(torch.int16)) and torch.equal(vc.view(torch.int16), vc2.view(torch.int16))
+    assert torch.equal(out[live], ref[live])
+    assert (out[~live] == 0).all()
