@@ -544,6 +544,36 @@ def main():
         comp_bytes = n_tok * (2048 + 8192 + 2048 + HKV * 4 * 4) + kept_pairs * 1024
         comps["compress_implied_gbs"] = comp_bytes / (ms_comp * 1e-3) / 1e9
 
+        # ---------------- the step in front of the path: fused q/k norm + sketch + RoPE ----------------
+        try:
+            from compactor_vllm.compression.compactor import approximate_leverage_scores
+            from compactor_vllm.layers.rotary_embedding import build_cos_sin_cache, fused_qk_norm_rope
+            cache = build_cos_sin_cache(D, 40960, 500000.0, ("llama3", 8.0, 1.0, 4.0, 8192)).to(dev)
+            pos = torch.arange(n_tok, device=dev)
+            qs, ks, _ = split_qkv(w.qkv)
+            nw = torch.ones(D, dtype=w.dtype, device=dev)
+            phi = getattr(w.cctx, "PHI", None)
+            if phi is None:
+                phi = (torch.randn((D, 48), device=dev) / 48 ** 0.5).to(w.dtype)
+            rope_bytes = n_tok * (HQ + HKV) * D * 2 * 2
+            ms_rope = max_over_ranks(time_loop(lambda: fused_qk_norm_rope(pos, qs, ks, cache), 10))
+            ms_fused = max_over_ranks(time_loop(
+                lambda: fused_qk_norm_rope(pos, qs, ks, cache, q_norm_weight=nw, k_norm_weight=nw, PHI=phi), 10))
+            comps["rope_ms"] = ms_rope
+            comps["rope_gbs"] = rope_bytes / (ms_rope * 1e-3) / 1e9
+            comps["norm_rope_sketch_ms"] = ms_fused
+            comps["norm_rope_sketch_gbs"] = (rope_bytes + n_tok * HKV * 96) / (ms_fused * 1e-3) / 1e9
+            sk = fused_qk_norm_rope(pos, qs, ks, cache, PHI=phi)[2]
+            lens = [n_tok]
+            comps["leverage_from_k_ms"] = max_over_ranks(time_loop(
+                lambda: approximate_leverage_scores(ks, lens, phi, normalize=True, chunk_size=512), 10))
+            comps["leverage_from_sketch_ms"] = max_over_ranks(time_loop(
+                lambda: approximate_leverage_scores(None, lens, phi, normalize=True, chunk_size=512,
+                                                    sketch_rows=sk), 10))
+            del cache, sk
+        except Exception as ex:
+            comps["prepath_error"] = repr(ex)[:200]
+
         # ---------------- decode on the compacted shape ----------------
         flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
         it = 40

@@ -47,6 +47,10 @@ _SIGNATURES = {
     "cvllm_leverage_scores_workspace_bytes": (_sz, [_i, _i, _i, _i]),
     "cvllm_leverage_scores": (_i, [_p, _i64, _i64, _p, _i, _i, _p, _p, _i, _i, _i, _i, _f, _i, _i,
                                    _p, _sz, _p]),
+    "cvllm_leverage_scores_from_sketch": (_i, [_p, _p, _i, _i, _p, _p, _i, _i, _i, _f, _i, _i, _p, _sz, _p]),
+    "cvllm_rope_qk": (_i, [_p, _p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i64, _i64, _i64, _p, _p, _i,
+                           _p, _p, _f, _p, _p, _i, _i, _i, _i, _i, _i, _p]),
+    "cvllm_rmsnorm": (_i, [_p, _p, _p, _p, _i64, _i64, _i64, _i, _i, _f, _i, _p]),
     "cvllm_chunk_attn_scores_workspace_bytes": (_sz, [_i, _i, _i, _i]),
     "cvllm_chunk_attn_scores": (_i, [_p, _p, _i64, _i64, _p, _i, _i, _i, _i, _i, _i, _i, _f, _i,
                                      _p, _i, _i64, _f, _p, _p, _p, _i, _p, _sz, _p]),

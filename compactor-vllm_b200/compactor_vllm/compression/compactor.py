@@ -29,6 +29,16 @@ class CompactorCompression(BaseCompressionMethod):
         )
 
     @staticmethod
+    def pre_rope_scoring_from_sketch(sketch_rows, context) -> Optional[torch.Tensor]:
+        """pre_rope_scoring for runners that call fused_qk_norm_rope (the sketch replaces k)."""
+        cc = context.compression_context
+        return maybe_execute_in_stream(
+            approximate_leverage_scores, None, cc.context_lens, cc.PHI, normalize=True,
+            chunk_size=cc.compression_chunk_size, sketch_rows=sketch_rows,
+            STORE_STREAM=context.STORE_STREAM,
+        )
+
+    @staticmethod
     def post_rope_scoring(q, k, v, pre_rope_scores, context) -> Optional[torch.Tensor]:
         cc = context.compression_context
         # The reference launches this on the main stream while pre_rope_scores is still being
@@ -102,14 +112,22 @@ def approximate_leverage_scores(
     regularizer: float = 5e-3,
     normalize: bool = False,
     chunk_size: int = 512,
+    *,
+    sketch_rows: Optional[torch.Tensor] = None,  # [N, H, k] = round(K.PHI) from fused_qk_norm_rope
 ) -> torch.Tensor:  # [N, H] in key_states.dtype
     """Randomised leverage scores of the pre-RoPE keys, per <=chunk_size chunk.
+
+    `sketch_rows` (extension): the sketch X = K.PHI already produced by the fused norm + RoPE
+    kernel (layers/rotary_embedding.py: fused_qk_norm_rope); `key_states` may then be None — the
+    normed pre-RoPE keys never exist in HBM on that route.  Same bits as the K route.
 
     Reference: compression/compactor.py:113-221: X = K.PHI, per chunk centre X,
     G = X^T X + reg*I, score_i = ||x_i V S^-1/2||^2 (== x_i^T G^-1 x_i), clamp
     >= 0, optional z-score per chunk across all heads (:215-220,224-269).
     Returned in K's dtype like the reference.
     """
+    if sketch_rows is not None:
+        return _leverage_from_sketch(sketch_rows, context_lens, regularizer, normalize, chunk_size)
     Ntok, H, D = key_states.shape
     assert key_states.stride(-1) == 1
     sketch = PHI.shape[1]
@@ -135,6 +153,32 @@ def approximate_leverage_scores(
         int(bool(normalize)), N.dtype_code(key_states.dtype), N.ptr(ws), ws.numel(), N.stream(dev),
     )
     N.check(rc, "cvllm_leverage_scores")
+    return out
+
+
+def _leverage_from_sketch(sketch_rows, context_lens, regularizer, normalize, chunk_size):
+    Ntok, H, sketch = sketch_rows.shape
+    assert sketch_rows.is_contiguous()
+    if chunk_size > 0:
+        _, chunk_lens = split_into_chunks(context_lens, chunk_size)
+    else:
+        chunk_lens = list(context_lens)
+    assert sum(chunk_lens) == Ntok
+    dev = sketch_rows.device
+    offsets = _chunk_offsets(tuple(chunk_lens), dev)
+    out = torch.empty((Ntok, H), dtype=sketch_rows.dtype, device=dev)
+    if Ntok == 0:
+        return out
+    n_chunks = len(chunk_lens)
+    L = N.lib()
+    ws_bytes = L.cvllm_leverage_scores_workspace_bytes(Ntok, H, sketch, n_chunks)
+    ws = N.workspace(dev, ws_bytes, "leverage")
+    rc = L.cvllm_leverage_scores_from_sketch(
+        N.ptr(sketch_rows), N.ptr(offsets), n_chunks, max(chunk_lens), None, N.ptr(out), Ntok, H, sketch,
+        float(regularizer), int(bool(normalize)), N.dtype_code(sketch_rows.dtype), N.ptr(ws), ws.numel(),
+        N.stream(dev),
+    )
+    N.check(rc, "cvllm_leverage_scores_from_sketch")
     return out
 
 

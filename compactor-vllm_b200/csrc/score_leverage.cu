@@ -35,6 +35,7 @@ struct LevParams {
   int64_t k_stride_n, k_stride_h;  // elements
   const int32_t* chunk_offsets;
   const void* phi;  // [128, 48] 16-bit
+  const void* sketch;  // optional [N, HKV, 48] 16-bit = round16(K.PHI) from rope.cu; null: derive it from k
   float* raw;       // [N, HKV] fp32 (values already rounded to 16-bit)
   float* gram;      // [n_chunks*HKV][48][48] fp32
   float* mean;      // [n_chunks*HKV][48] fp32
@@ -75,6 +76,25 @@ __device__ __forceinline__ void sketch_tile(LevSmem& sm, const LevParams& p, int
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, r = lane >> 2, j = lane & 3;
   const char* kb = reinterpret_cast<const char*>(p.k);
   const int n_mt = (nt + 15) / 16;
+  if (p.sketch) {
+    // precomputed sketch rows (96 B per (token, head)): transpose into xt, zero the m-tile padding
+    const uint16_t* xs = reinterpret_cast<const uint16_t*>(p.sketch);
+    const int nt16 = n_mt * 16;
+    for (int i = threadIdx.x; i < nt16 * (kSk / 8); i += kLevThreads) {
+      const int cchunk = i / nt16, t = i - cchunk * nt16;
+      uint4 v = make_uint4(0, 0, 0, 0);
+      if (t < nt) v = *reinterpret_cast<const uint4*>(xs + ((int64_t)(tok0 + t) * p.HKV + h) * kSk + cchunk * 8);
+      const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        uint16_t bits = (uint16_t)(w[e >> 1] >> ((e & 1) * 16));
+        if (centre && t < nt)
+          bits = to16<BF16>(round16<BF16>(from16<BF16>(bits) - sm.mean[cchunk * 8 + e]));
+        sm.xt[cchunk * 8 + e][t] = bits;
+      }
+    }
+    return;
+  }
   for (int mt = warp; mt < n_mt; mt += kLevThreads / 32) {
     const int t_lo = mt * 16 + r, t_hi = t_lo + 8;
     auto krow = [&](int t) -> const char* {
@@ -133,7 +153,7 @@ __global__ void __launch_bounds__(kLevThreads, 2) leverage_gram_kernel(const Lev
   if (c_len <= 0) return;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
-  load_phi(sm, p);
+  if (!p.sketch) load_phi(sm, p);
   if (tid < kSk) sm.colsum[tid] = 0.f;
   for (int i = tid; i < kSk * (kSk + 1); i += kLevThreads) (&sm.g[0][0])[i] = 0.f;
   __syncthreads();
@@ -420,7 +440,7 @@ __global__ void __launch_bounds__(kLevThreads, 2) leverage_score_kernel(const Le
   const int c_beg = p.chunk_offsets[ch], c_len = p.chunk_offsets[ch + 1] - c_beg;
   if (c_len <= 0) return;
   const int tid = threadIdx.x;
-  load_phi(sm, p);
+  if (!p.sketch) load_phi(sm, p);
   {
     const float* svin = p.sv + (int64_t)(ch * p.HKV + h) * kSk * kSk;
     for (int i = tid; i < kSk * kSk; i += kLevThreads) (&sm.sv[0][0])[i] = svin[i];
@@ -514,24 +534,24 @@ extern "C" size_t cvllm_leverage_scores_workspace_bytes(int N, int HKV, int sket
          lev_align(mats * kSk * sizeof(float));
 }
 
-extern "C" int cvllm_leverage_scores(const void* k_pre, int64_t k_stride_n, int64_t k_stride_h,
-                                     const int32_t* chunk_offsets, int n_chunks, int max_chunk,
-                                     const void* phi, void* out_scores, int N, int HKV, int D, int sketch,
-                                     float regularizer, int normalize, int dtype, void* workspace,
-                                     size_t workspace_bytes, cvllm_stream_t stream) {
+static int leverage_launch(const void* k_pre, int64_t k_stride_n, int64_t k_stride_h, const void* sketch_rows,
+                           const int32_t* chunk_offsets, int n_chunks, int max_chunk,
+                           const void* phi, void* out_scores, int N, int HKV, int D, int sketch,
+                           float regularizer, int normalize, int dtype, void* workspace,
+                           size_t workspace_bytes, cvllm_stream_t stream) {
   CVLLM_CHECK_ARG(N >= 0 && HKV > 0 && n_chunks >= 0 && max_chunk >= 0);
   if (N == 0 || n_chunks == 0) return CVLLM_OK;
-  CVLLM_CHECK_ARG(k_pre && chunk_offsets && phi && out_scores && workspace);
+  CVLLM_CHECK_ARG((sketch_rows || (k_pre && phi)) && chunk_offsets && out_scores && workspace);
   CVLLM_CHECK_ARG(dtype == CVLLM_F16 || dtype == CVLLM_BF16);
   CVLLM_CHECK_SUPPORTED(D == 128 && sketch == kSk);
-  CVLLM_CHECK_ALIGN(aligned16(k_pre) && k_stride_n % 8 == 0 && k_stride_h % 8 == 0);
+  CVLLM_CHECK_ALIGN(aligned16(k_pre) && aligned16(sketch_rows) && k_stride_n % 8 == 0 && k_stride_h % 8 == 0);
   CVLLM_CHECK_ARG(workspace_bytes >= cvllm_leverage_scores_workspace_bytes(N, HKV, sketch, n_chunks));
   auto st = static_cast<cudaStream_t>(stream);
   const size_t mats = (size_t)n_chunks * HKV;
   char* wsb = reinterpret_cast<char*>(workspace);
   LevParams p;
   p.k = k_pre; p.k_stride_n = k_stride_n; p.k_stride_h = k_stride_h; p.chunk_offsets = chunk_offsets;
-  p.phi = phi; p.HKV = HKV; p.reg = regularizer;
+  p.phi = phi; p.sketch = sketch_rows; p.HKV = HKV; p.reg = regularizer;
   p.raw = reinterpret_cast<float*>(wsb);
   wsb += lev_align((size_t)N * HKV * sizeof(float));
   p.gram = reinterpret_cast<float*>(wsb);
@@ -564,4 +584,26 @@ extern "C" int cvllm_leverage_scores(const void* k_pre, int64_t k_stride_n, int6
   }
   CVLLM_CHECK_LAUNCHES(4);
   return CVLLM_OK;
+}
+
+extern "C" int cvllm_leverage_scores(const void* k_pre, int64_t k_stride_n, int64_t k_stride_h,
+                                     const int32_t* chunk_offsets, int n_chunks, int max_chunk,
+                                     const void* phi, void* out_scores, int N, int HKV, int D, int sketch,
+                                     float regularizer, int normalize, int dtype, void* workspace,
+                                     size_t workspace_bytes, cvllm_stream_t stream) {
+  if (N > 0 && n_chunks > 0) CVLLM_CHECK_ARG(k_pre != nullptr);
+  return leverage_launch(k_pre, k_stride_n, k_stride_h, nullptr, chunk_offsets, n_chunks, max_chunk, phi,
+                         out_scores, N, HKV, D, sketch, regularizer, normalize, dtype, workspace,
+                         workspace_bytes, stream);
+}
+
+extern "C" int cvllm_leverage_scores_from_sketch(const void* sketch_rows, const int32_t* chunk_offsets,
+                                                 int n_chunks, int max_chunk, const void* phi,
+                                                 void* out_scores, int N, int HKV, int sketch,
+                                                 float regularizer, int normalize, int dtype,
+                                                 void* workspace, size_t workspace_bytes,
+                                                 cvllm_stream_t stream) {
+  if (N > 0 && n_chunks > 0) CVLLM_CHECK_ARG(sketch_rows != nullptr);
+  return leverage_launch(nullptr, 0, 0, sketch_rows, chunk_offsets, n_chunks, max_chunk, phi, out_scores, N,
+                         HKV, 128, sketch, regularizer, normalize, dtype, workspace, workspace_bytes, stream);
 }

@@ -199,6 +199,46 @@ int cvllm_leverage_scores(const void* k_pre, int64_t k_stride_n, int64_t k_strid
                           const void* phi, void* out_scores, int N, int HKV, int D,
                           int sketch, float regularizer, int normalize, int dtype,
                           void* workspace, size_t workspace_bytes, cvllm_stream_t stream);
+/* Same chain from a precomputed sketch: sketch_rows [N, HKV, 48] in `dtype`
+ * = round16(K_pre . PHI) — compression/compactor.py:153-158 — as written by
+ * cvllm_rope_qk; bit-identical scores to cvllm_leverage_scores on the same
+ * keys.  phi may be NULL. */
+int cvllm_leverage_scores_from_sketch(const void* sketch_rows, const int32_t* chunk_offsets,
+                                      int n_chunks, int max_chunk, const void* phi,
+                                      void* out_scores, int N, int HKV, int sketch,
+                                      float regularizer, int normalize, int dtype,
+                                      void* workspace, size_t workspace_bytes,
+                                      cvllm_stream_t stream);
+
+/* ------------------------------------------------------------------------
+ * The step in front of the path
+ * --------------------------------------------------------------------- */
+
+/* RotaryEmbedding.forward — layers/rotary_embedding.py:69-80 (neox
+ * rotate-half, :8-16), optionally preceded by the per-head q_norm / k_norm
+ * RMSNorm of models/qwen3.py:90-91 (layers/layernorm.py:16-26) and emitting
+ * the Compactor sketch of the (normed) pre-RoPE keys
+ * (compression/compactor.py:153-158) in the same pass.
+ *   q [N,HQ,128], k [N,HKV,128] strided; q_out / k_out may alias q / k
+ *   positions int64 [N]; cos_sin_cache fp32 [max_position, 128] = cos | sin
+ *   q_norm_weight / k_norm_weight: [128] in `dtype` or NULL (no norm)
+ *   phi [128,48] in `dtype` + sketch_out [N,HKV,48] in `dtype`, or both NULL
+ *   (sketch needs HKV <= 8) */
+int cvllm_rope_qk(const void* q, const void* k, void* q_out, void* k_out, int64_t q_stride_n,
+                  int64_t q_stride_h, int64_t k_stride_n, int64_t k_stride_h,
+                  int64_t qo_stride_n, int64_t qo_stride_h, int64_t ko_stride_n,
+                  int64_t ko_stride_h, const int64_t* positions, const float* cos_sin_cache,
+                  int max_position, const void* q_norm_weight, const void* k_norm_weight,
+                  float eps, const void* phi, void* sketch_out, int N, int HQ, int HKV, int D,
+                  int sketch, int dtype, cvllm_stream_t stream);
+
+/* RMSNorm.forward — layers/layernorm.py:16-49.  residual == NULL:
+ * out = round16(x * rsqrt(mean(x^2) + eps)) * weight.  residual != NULL
+ * (add_rms_forward): x += residual in fp32, residual <- round16(x) in place,
+ * then the same norm.  width % 8 == 0, width <= 8192. */
+int cvllm_rmsnorm(const void* x, void* residual, const void* weight, void* out, int64_t x_stride,
+                  int64_t residual_stride, int64_t out_stride, int rows, int width, float eps,
+                  int dtype, cvllm_stream_t stream);
 
 /* non_causal_attn_scores — compression/compactor.py:338-599.  Chunk-local
  * softmax column sums, per-sequence z-score, + blend*accum, protected

@@ -345,9 +345,48 @@ def gen_leverage():
         cp.torch.linalg.svd = real_svd
 
 
+def gen_prepath():
+    """The reference's RotaryEmbedding / RMSNorm modules, eager (TorchDynamo disabled: their
+    forward methods are torch.compile'd, which would need a CUDA-free inductor build here)."""
+    import torch._dynamo
+    torch._dynamo.config.disable = True
+    from compactor_vllm.layers.layernorm import RMSNorm
+    from compactor_vllm.layers.rotary_embedding import RotaryEmbedding
+
+    gen = torch.Generator().manual_seed(77)
+    D, HQ, HKV, Ntok, max_pos = 128, 8, 2, 37, 512
+    for name, dtype, scaling, base in [
+        ("rope_bf16_llama3", torch.bfloat16, ("llama3", 8.0, 1.0, 4.0, 64), 500000.0),
+        ("rope_f16_plain", torch.float16, None, 10000.0),
+    ]:
+        rope = RotaryEmbedding(D, D, max_pos, base, scaling)
+        q = torch.randn((Ntok, HQ, D), generator=gen).to(dtype)
+        k = torch.randn((Ntok, HKV, D), generator=gen).to(dtype)
+        pos = torch.randint(0, max_pos, (Ntok,), generator=gen)
+        qo, ko = rope(pos, q, k)
+        save(name, q=q, k=k, positions=pos, cos_sin_cache=rope.cos_sin_cache.view(max_pos, D),
+             q_out=qo, k_out=ko, base=np.array(base),
+             scaling=np.array(list(scaling[1:]) if scaling else [], dtype=np.float64))
+    for name, dtype, width, rows in [("rmsnorm_bf16_128", torch.bfloat16, 128, 45),
+                                     ("rmsnorm_bf16_4096", torch.bfloat16, 4096, 9),
+                                     ("rmsnorm_f16_1024", torch.float16, 1024, 5)]:
+        norm = RMSNorm(width, eps=1e-6)
+        with torch.no_grad():
+            norm.weight.copy_(1.0 + 0.2 * torch.randn(width, generator=gen))
+        norm = norm.to(dtype)
+        x = (2.0 * torch.randn((rows, width), generator=gen)).to(dtype)
+        res = torch.randn((rows, width), generator=gen).to(dtype)
+        with torch.no_grad():
+            y = norm(x.clone())
+            y2, r2 = norm(x.clone(), res.clone())
+        save(name, x=x, residual=res, weight=norm.weight.detach(), y=y, y_add=y2, residual_out=r2,
+             eps=np.array(1e-6))
+
+
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["prefill", "decode", "stores", "chunk", "snapkv", "leverage"]
+    which = sys.argv[1:] or ["prefill", "decode", "stores", "chunk", "snapkv", "leverage", "prepath"]
     table = {"prefill": gen_prefill, "decode": gen_decode, "stores": gen_stores,
-             "chunk": gen_chunk_scores, "snapkv": gen_snapkv, "leverage": gen_leverage}
+             "chunk": gen_chunk_scores, "snapkv": gen_snapkv, "leverage": gen_leverage,
+             "prepath": gen_prepath}
     for w in which:
         table[w]()

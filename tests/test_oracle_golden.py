@@ -172,3 +172,34 @@ def test_leverage_matches_reference(name):
     mine = set(torch.topk(norm.float().flatten(), k).indices.tolist())
     ref = set(torch.topk(g["norm"].float().flatten(), k).indices.tolist())
     assert len(mine & ref) / k >= 0.99
+
+
+# ---- the step in front of the path: RoPE / RMSNorm, reference modules run eager ----
+@pytest.mark.parametrize("name", ["rope_bf16_llama3", "rope_f16_plain"])
+def test_rope_oracle_and_cache_match_reference(name):
+    from oracle import prepath as op
+    from compactor_vllm.layers.rotary_embedding import build_cos_sin_cache
+
+    g = load_golden(name)
+    scaling = tuple(["llama3", *[float(x) for x in g["scaling"]]]) if len(g["scaling"]) else None
+    if scaling is not None:
+        scaling = (scaling[0], scaling[1], scaling[2], scaling[3], int(scaling[4]))
+    max_pos, D = g["cos_sin_cache"].shape
+    # the oracle's and the product's cache builders both reproduce the reference's buffer
+    assert torch.equal(op.cos_sin_cache(D, max_pos, g["base"], scaling), g["cos_sin_cache"])
+    assert torch.equal(build_cos_sin_cache(D, max_pos, g["base"], scaling).view(max_pos, D), g["cos_sin_cache"])
+    qo, ko, _ = op.fused_qk_norm_rope(g["positions"], g["q"], g["k"], g["cos_sin_cache"])
+    assert torch.equal(qo.view(torch.int16), g["q_out"].view(torch.int16))
+    assert torch.equal(ko.view(torch.int16), g["k_out"].view(torch.int16))
+
+
+@pytest.mark.parametrize("name", ["rmsnorm_bf16_128", "rmsnorm_bf16_4096", "rmsnorm_f16_1024"])
+def test_rmsnorm_oracle_matches_reference(name):
+    from oracle import prepath as op
+
+    g = load_golden(name)
+    y = op.rms_norm(g["x"], g["weight"], g["eps"])
+    assert torch.equal(y.view(torch.int16), g["y"].view(torch.int16))
+    y2, r2 = op.rms_norm(g["x"], g["weight"], g["eps"], g["residual"])
+    assert torch.equal(y2.view(torch.int16), g["y_add"].view(torch.int16))
+    assert torch.equal(r2.view(torch.int16), g["residual_out"].view(torch.int16))
