@@ -27,6 +27,11 @@ _SIGNATURES = {
     "cvllm_prefill_store_all": (_i, [_p, _p, _i64, _i64, _i64, _i64, _p, _p, _p, _p, _p, _p,
                                      _i, _i, _i, _i, _i, _i, _i, _p]),
     "cvllm_scatter_pages": (_i, [_p, _p, _p, _p, _i64, _i64, _i64, _i, _i, _i, _p]),
+    "cvllm_pages_bitmap_words": (_sz, [_i]),
+    "cvllm_pages_workspace_bytes": (_sz, [_i, _i, _i, _i, _i]),
+    "cvllm_pages_init": (_i, [_p, _p, _i, _i, _p]),
+    "cvllm_pages_reserve": (_i, [_p, _p, _p, _p, _p, _p, _i, _i, _p, _i, _i, _i, _i, _i, _i, _i, _p, _sz, _p]),
+    "cvllm_pages_release": (_i, [_p, _p, _p, _p, _p, _p, _i, _i, _i, _p, _i, _i, _i, _i, _i, _i, _i, _p]),
     "cvllm_rank_scores_workspace_bytes": (_sz, [_i, _i, _i]),
     "cvllm_rank_scores": (_i, [_p, _i64, _p, _i, _i, _i, _i, _p, _p, _sz, _p]),
     "cvllm_store_topk_workspace_bytes": (_sz, [_i, _i, _i, _i]),

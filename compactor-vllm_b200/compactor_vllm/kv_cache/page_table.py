@@ -168,3 +168,118 @@ class PagedKVCache(torch.nn.Module):
             self.kv_cache[0, layer], self.kv_cache[1, layer],
             self.page_table[layer], self.bh_seq_lens[layer],
         )
+
+
+class DevicePagedKVCache(PagedKVCache):
+    """PagedKVCache whose page allocator lives on the GPU (csrc/page_alloc.cu).
+
+    Same constructor, methods, return values and — bit for bit — the same page ids as the host
+    allocator above (and the reference's heaps): the free set of a layer is a bitmap, "pop the n
+    smallest pages" a popcount scan.  reserve / reclaim / free are stream-ordered launches:
+
+    * `reserve_tokens_device(slots, add_tokens, status=None)` / `reclaim_pages_device(slots, future)`
+      take a DEVICE int32 vector of slots (entries equal to RESERVED_BATCH are skipped), never touch
+      the host and can be captured in a CUDA graph next to the decode step — the reference pays two
+      device->host syncs, a Python heap loop and a host->device copy per reservation
+      (kv_cache/page_table.py:160-182) and cannot reclaim per layer under TP at all
+      (core/model_runner.py:287-291);
+    * the reference-shaped `reserve_tokens` / `reclaim_pages` / `new_batch` wrap them and read back
+      4-8 bytes (the status / freed count / free counts) because their signatures return host values.
+
+    Slots (`free_batches`) stay a host list: the engine hands them out on the host.
+    """
+
+    def __init__(self, *args, **kwargs):
+        super().__init__(*args, **kwargs)
+        from compactor_vllm import _native as N
+        self._N = N
+        dev = self.page_table.device
+        assert dev.type == "cuda", "the device allocator has no CPU fallback"
+        L = self.num_layers
+        self._words = int(N.lib().cvllm_pages_bitmap_words(self.n_pages))
+        self.free_bits = torch.empty((L, self._words), dtype=torch.int32, device=dev)
+        self.free_count = torch.empty((L,), dtype=torch.int32, device=dev)
+        self._freed = torch.zeros((1,), dtype=torch.int64, device=dev)
+        self._status1 = torch.zeros((1,), dtype=torch.int32, device=dev)
+        self._slot1 = torch.zeros((1,), dtype=torch.int32, device=dev)
+        N.check(N.lib().cvllm_pages_init(N.ptr(self.free_bits), N.ptr(self.free_count), L, self.n_pages,
+                                         N.stream(dev)), "cvllm_pages_init")
+        # the host structures of the base class are not maintained
+        self.pages_indices_per_batch = None
+
+    # -- device-resident API (no host sync, graph-capturable) -------------------
+    def reserve_tokens_device(self, slots: torch.Tensor, add_tokens: int,
+                              status: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """slots int32 [nb] on the device -> status int32 [nb] (0 ok, 1 too long, 2 out of pages)."""
+        N = self._N
+        nb = slots.numel()
+        assert slots.dtype == torch.int32 and slots.is_contiguous()
+        if status is None:
+            status = torch.empty((nb,), dtype=torch.int32, device=slots.device)
+        L, Bs, H, P = self.page_table.shape
+        lib = N.lib()
+        ws_bytes = lib.cvllm_pages_workspace_bytes(L, H, P, self.n_pages, nb)
+        ws = N.workspace(slots.device, ws_bytes, "pages")
+        rc = lib.cvllm_pages_reserve(
+            N.ptr(self.free_bits), N.ptr(self.free_count), N.ptr(self.page_table), N.ptr(self.bh_seq_lens),
+            N.ptr(self.bh_num_pages), N.ptr(slots), nb, int(add_tokens), N.ptr(status), L, Bs, H, P,
+            self.page_size, self.n_pages, RESERVED_BATCH, N.ptr(ws), ws.numel(), N.stream(slots.device))
+        N.check(rc, "cvllm_pages_reserve")
+        return status
+
+    def _release(self, slots: torch.Tensor, future: int, free_all: bool, count: bool) -> None:
+        N = self._N
+        L, Bs, H, P = self.page_table.shape
+        rc = N.lib().cvllm_pages_release(
+            N.ptr(self.free_bits), N.ptr(self.free_count), N.ptr(self.page_table), N.ptr(self.bh_seq_lens),
+            N.ptr(self.bh_num_pages), N.ptr(slots), slots.numel(), int(future), int(free_all),
+            N.ptr(self._freed) if count else None, L, Bs, H, P, self.page_size, self.n_pages, RESERVED_BATCH,
+            N.stream(slots.device))
+        N.check(rc, "cvllm_pages_release")
+
+    def reclaim_pages_device(self, slots: torch.Tensor, future_reserve_tokens: int = 0) -> None:
+        assert slots.dtype == torch.int32 and slots.is_contiguous()
+        self._release(slots, future_reserve_tokens, False, False)
+
+    # -- reference-shaped API -----------------------------------------------------
+    def new_batch(self) -> Optional[int]:
+        if self.free_batches and int(self.free_count.min()) >= self.H_kv:
+            return self.free_batches.pop()
+        return None
+
+    def reserve_tokens(self, batch_index: int, add_tokens: int) -> KVAllocationStatus:
+        self._slot1.fill_(int(batch_index))
+        code = int(self.reserve_tokens_device(self._slot1, add_tokens, self._status1))
+        return (KVAllocationStatus.SUCCESS, KVAllocationStatus.EXCEEDS_MAX_SEQUENCE_LENGTH,
+                KVAllocationStatus.EXCEEDS_CURRENTLY_AVAILABLE_PAGES)[code]
+
+    def reclaim_pages(self, batch_index: int, future_reserve_tokens: int = 0) -> int:
+        assert 0 <= batch_index < self.max_num_batches
+        self._slot1.fill_(int(batch_index))
+        self._freed.zero_()
+        self._release(self._slot1, future_reserve_tokens, False, True)
+        return int(self._freed) * self.page_size * self.head_dim * self.kv_cache.element_size() * 2
+
+    def free_batch(self, batch_index: int) -> None:
+        self._slot1.fill_(int(batch_index))
+        self._release(self._slot1, 0, True, False)
+        self.free_batches.append(batch_index)
+
+    @property
+    def free_pages(self) -> List[List[int]]:
+        """Sorted free page ids per layer, decoded from the bitmap (tests / introspection: syncs)."""
+        bits = self.free_bits.cpu().numpy().view("uint32")
+        out = []
+        for l in range(self.num_layers):
+            ids = []
+            for w, word in enumerate(bits[l].tolist()):
+                while word:
+                    low = word & -word
+                    ids.append(w * 32 + low.bit_length() - 1)
+                    word ^= low
+            out.append(ids)
+        return out
+
+    @free_pages.setter
+    def free_pages(self, value) -> None:  # the base constructor assigns its host heaps; dropped here
+        pass

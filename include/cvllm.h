@@ -88,6 +88,41 @@ int cvllm_scatter_pages(const int32_t* add_pages, const int32_t* new_phys,
                         int L, int H, int max_pages_per_head, cvllm_stream_t stream);
 
 /* ------------------------------------------------------------------------
+ * Device-side page allocator — PagedKVCache.reserve_tokens /
+ * reclaim_pages / free_batch, kv_cache/page_table.py:144-291, without the
+ * host heaps: the free set of a layer is a bitmap (bit set = page free), "pop
+ * the n smallest ids" is a popcount scan.  Same page ids as the reference's
+ * min-heaps.  page_table int32 [L, num_slots, H, P]; bh_seq_lens /
+ * bh_num_pages int32 [L, num_slots, H]; free_bits uint32 [L, words];
+ * free_count int32 [L]; slots int32 [nb] (entries == reserved_batch are
+ * skipped); sequences of one call are served in order.
+ * --------------------------------------------------------------------- */
+enum {
+  CVLLM_PAGES_OK = 0,
+  CVLLM_PAGES_EXCEEDS_MAX_SEQUENCE_LENGTH = 1,
+  CVLLM_PAGES_EXCEEDS_AVAILABLE_PAGES = 2
+};
+size_t cvllm_pages_bitmap_words(int n_pages);
+size_t cvllm_pages_workspace_bytes(int L, int H, int P, int n_pages, int nb);
+int cvllm_pages_init(uint32_t* free_bits, int32_t* free_count, int L, int n_pages,
+                     cvllm_stream_t stream);
+/* status int32 [nb] <- CVLLM_PAGES_*; a sequence that fails takes nothing
+ * (all-or-nothing across layers, page_table.py:171-176). */
+int cvllm_pages_reserve(uint32_t* free_bits, int32_t* free_count, int32_t* page_table,
+                        const int32_t* bh_seq_lens, int32_t* bh_num_pages, const int32_t* slots,
+                        int nb, int add_tokens, int32_t* status, int L, int num_slots, int H,
+                        int P, int PS, int n_pages, int reserved_batch, void* workspace,
+                        size_t workspace_bytes, cvllm_stream_t stream);
+/* free_all == 0: reclaim_pages (keep ceil((len + future_tokens)/PS) pages per
+ * head); free_all != 0: free_batch (all pages back, lens and counts zeroed).
+ * freed_pages_out (may be NULL) is incremented by the pages returned. */
+int cvllm_pages_release(uint32_t* free_bits, int32_t* free_count, const int32_t* page_table,
+                        int32_t* bh_seq_lens, int32_t* bh_num_pages, const int32_t* slots, int nb,
+                        int future_tokens, int free_all, unsigned long long* freed_pages_out,
+                        int L, int num_slots, int H, int P, int PS, int n_pages,
+                        int reserved_batch, cvllm_stream_t stream);
+
+/* ------------------------------------------------------------------------
  * Selection + compaction
  * --------------------------------------------------------------------- */
 

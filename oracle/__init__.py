@@ -18,4 +18,4 @@ reference's torch code path re-executed on CPU with torch.linalg.svd
 substituted for the gesvda driver — see gen_golden.py; that substitution means
 leverage parity is "pinned to the reference formula, not to cuSOLVER's bits".
 """
-from . import attention, prepath, scoring, selection, store  # noqa: F401
+from . import allocator, attention, prepath, scoring, selection, store  # noqa: F401

@@ -29,6 +29,7 @@ import sys
 os.environ["TRITON_INTERPRET"] = "1"
 REF_SRC = os.environ.get("CVLLM_REFERENCE_SRC", "/root/reference/src")
 sys.path.insert(0, REF_SRC)
+sys.path.insert(1, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))  # repo root: oracle.gen_golden_script
 
 from pathlib import Path  # noqa: E402
 
@@ -383,10 +384,65 @@ def gen_prepath():
              eps=np.array(1e-6))
 
 
+from oracle.gen_golden_script import ALLOC_SCRIPT, ALLOC_SHAPE, alloc_lens  # noqa: E402
+
+
+def gen_allocator():
+    """The reference's PagedKVCache driven on CPU: `device="cuda"` of the one torch.tensor call in
+    reserve_tokens (kv_cache/page_table.py:182) redirected to CPU, the Triton page scatter interpreted."""
+    from compactor_vllm.kv_cache import page_table as ptm
+
+    real_tensor, real_empty = torch.tensor, torch.empty
+
+    def on_cpu(fn):
+        def wrapped(*a, **k):
+            if k.get("device") == "cuda":
+                k["device"] = "cpu"
+            return fn(*a, **k)
+        return wrapped
+
+    # page_table.py:182 and write_page_table.py's cumsum scratch name device="cuda" literally
+    torch.tensor, torch.empty = on_cpu(real_tensor), on_cpu(real_empty)
+    try:
+        cache = ptm.PagedKVCache(dtype=torch.float16, device="cpu", **ALLOC_SHAPE)
+        L, H, P = ALLOC_SHAPE["num_layers"], ALLOC_SHAPE["H_kv"], ALLOC_SHAPE["max_logical_pages_per_head"]
+        status_code = {ptm.KVAllocationStatus.SUCCESS: 0, ptm.KVAllocationStatus.EXCEEDS_MAX_SEQUENCE_LENGTH: 1,
+                       ptm.KVAllocationStatus.EXCEEDS_CURRENTLY_AVAILABLE_PAGES: 2}
+        slots, rets, pts, pages, lens, frees = {}, [], [], [], [], []
+        for op, name, arg in ALLOC_SCRIPT:
+            ret = -1
+            if op == "new":
+                s = cache.new_batch()
+                slots[name] = s
+                ret = -1 if s is None else s
+            elif op == "reserve":
+                ret = status_code[cache.reserve_tokens(slots[name], arg)]
+            elif op == "lens":
+                cache.bh_seq_lens[:, slots[name]] = alloc_lens(arg, L, H, cache.bh_num_pages[:, slots[name]])
+            elif op == "reclaim":
+                ret = cache.reclaim_pages(slots[name], arg)
+            elif op == "free":
+                cache.free_batch(slots[name])
+            rets.append(ret)
+            valid = torch.arange(P).view(1, 1, 1, P) < cache.bh_num_pages.unsqueeze(-1)
+            pts.append(torch.where(valid, cache.page_table, torch.full_like(cache.page_table, -1)).clone())
+            pages.append(cache.bh_num_pages.clone())
+            lens.append(cache.bh_seq_lens.clone())
+            fr = torch.full((L, ALLOC_SHAPE["num_pages"]), -1, dtype=torch.int32)
+            for l in range(L):
+                f = sorted(cache.free_pages[l])
+                fr[l, :len(f)] = torch.tensor(f, dtype=torch.int32)
+            frees.append(fr)
+        save("allocator_trace", rets=torch.tensor(rets, dtype=torch.int64), page_table=torch.stack(pts),
+             bh_num_pages=torch.stack(pages), bh_seq_lens=torch.stack(lens), free_pages=torch.stack(frees))
+    finally:
+        torch.tensor, torch.empty = real_tensor, real_empty
+
+
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["prefill", "decode", "stores", "chunk", "snapkv", "leverage", "prepath"]
+    which = sys.argv[1:] or ["prefill", "decode", "stores", "chunk", "snapkv", "leverage", "prepath", "allocator"]
     table = {"prefill": gen_prefill, "decode": gen_decode, "stores": gen_stores,
              "chunk": gen_chunk_scores, "snapkv": gen_snapkv, "leverage": gen_leverage,
-             "prepath": gen_prepath}
+             "prepath": gen_prepath, "allocator": gen_allocator}
     for w in which:
         table[w]()

@@ -203,3 +203,61 @@ def test_rmsnorm_oracle_matches_reference(name):
     y2, r2 = op.rms_norm(g["x"], g["weight"], g["eps"], g["residual"])
     assert torch.equal(y2.view(torch.int16), g["y_add"].view(torch.int16))
     assert torch.equal(r2.view(torch.int16), g["residual_out"].view(torch.int16))
+
+
+# ---- page allocator: the reference's PagedKVCache driven on CPU through oracle.gen_golden.ALLOC_SCRIPT ----
+def replay_allocator_script(make, set_lens):
+    """Run the scripted op sequence on an allocator-like object; yields (step, ret) after each op.
+    `make()` builds it, `set_lens(obj, slot, lens[L,H])` overwrites the slot's lengths."""
+    from oracle.gen_golden_script import ALLOC_SCRIPT, ALLOC_SHAPE, alloc_lens
+
+    obj = make(ALLOC_SHAPE)
+    slots = {}
+    for step, (op, name, arg) in enumerate(ALLOC_SCRIPT):
+        ret = -1
+        if op == "new":
+            s = obj.new_batch()
+            slots[name] = s
+            ret = -1 if s is None else s
+        elif op == "reserve":
+            ret = obj.reserve_tokens(slots[name], arg)
+        elif op == "lens":
+            set_lens(obj, slots[name], arg)
+        elif op == "reclaim":
+            ret = obj.reclaim_pages(slots[name], arg)
+        elif op == "free":
+            obj.free_batch(slots[name])
+        yield step, obj, ret
+
+
+def test_allocator_oracle_matches_reference_trace():
+    from oracle import allocator as oal
+    from oracle.gen_golden_script import ALLOC_SHAPE, alloc_lens
+
+    g = load_golden("allocator_trace")
+    L, H, PS = ALLOC_SHAPE["num_layers"], ALLOC_SHAPE["H_kv"], ALLOC_SHAPE["page_size"]
+
+    def make(shape):
+        return oal.Allocator(shape["num_layers"], shape["max_logical_pages_per_head"], shape["num_pages"],
+                             shape["page_size"], shape["H_kv"], shape["max_num_batches"])
+
+    def set_lens(a, slot, seed):
+        cap = torch.tensor([[a.pages[l][slot][h] for h in range(H)] for l in range(L)], dtype=torch.int32)
+        new = alloc_lens(seed, L, H, cap)
+        for l in range(L):
+            for h in range(H):
+                a.lens[l][slot][h] = int(new[l, h])
+
+    page_bytes = PS * ALLOC_SHAPE["head_dim"] * 2 * 2
+    for step, a, ret in replay_allocator_script(make, set_lens):
+        want = int(g["rets"][step])
+        from oracle.gen_golden_script import ALLOC_SCRIPT
+        if ALLOC_SCRIPT[step][0] == "reclaim":
+            ret *= page_bytes  # the reference reports bytes (K + V) freed, the oracle pages
+        assert ret == want, (step, ALLOC_SCRIPT[step], ret, want)
+        pt, pages, lens, free = a.snapshot()
+        assert np.array_equal(pt, g["page_table"][step].numpy()), step
+        assert np.array_equal(pages, g["bh_num_pages"][step].numpy()), step
+        assert np.array_equal(lens, g["bh_seq_lens"][step].numpy()), step
+        gf = g["free_pages"][step].numpy()
+        assert np.array_equal(free, gf[:, :free.shape[1]]) and (gf[:, free.shape[1]:] == -1).all(), step
