@@ -285,6 +285,21 @@ def time_loop(fn, iters: int, flush=None) -> float:
     return tot / iters
 
 
+def time_batch(fn, reps: int = 10) -> float:
+    """Average ms per call of `reps` back-to-back calls inside ONE event pair: for kernels shorter than the
+    Python launch path (the launches queue up, so the device, not the host, sets the pace)."""
+    for _ in range(2):
+        fn()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    a.record()
+    for _ in range(reps):
+        fn()
+    b.record()
+    b.synchronize()
+    return a.elapsed_time(b) / reps
+
+
 def decode_bench(device, dtype, B: int, lens_bh: torch.Tensor, iters: int, flush, seed: int):
     """One decode step = decode_store_kv + head_sparse_decode_attention on a synthetic compacted cache,
     captured in a CUDA graph and replayed (how the reference engine runs decode, core/model_runner.py:524-528);
@@ -556,23 +571,50 @@ def main():
             if phi is None:
                 phi = (torch.randn((D, 48), device=dev) / 48 ** 0.5).to(w.dtype)
             rope_bytes = n_tok * (HQ + HKV) * D * 2 * 2
-            ms_rope = max_over_ranks(time_loop(lambda: fused_qk_norm_rope(pos, qs, ks, cache), 10))
-            ms_fused = max_over_ranks(time_loop(
-                lambda: fused_qk_norm_rope(pos, qs, ks, cache, q_norm_weight=nw, k_norm_weight=nw, PHI=phi), 10))
+            ms_rope = max_over_ranks(time_batch(lambda: fused_qk_norm_rope(pos, qs, ks, cache), 20))
+            ms_fused = max_over_ranks(time_batch(
+                lambda: fused_qk_norm_rope(pos, qs, ks, cache, q_norm_weight=nw, k_norm_weight=nw, PHI=phi), 20))
             comps["rope_ms"] = ms_rope
             comps["rope_gbs"] = rope_bytes / (ms_rope * 1e-3) / 1e9
             comps["norm_rope_sketch_ms"] = ms_fused
             comps["norm_rope_sketch_gbs"] = (rope_bytes + n_tok * HKV * 96) / (ms_fused * 1e-3) / 1e9
             sk = fused_qk_norm_rope(pos, qs, ks, cache, PHI=phi)[2]
             lens = [n_tok]
-            comps["leverage_from_k_ms"] = max_over_ranks(time_loop(
+            comps["leverage_from_k_ms"] = max_over_ranks(time_batch(
                 lambda: approximate_leverage_scores(ks, lens, phi, normalize=True, chunk_size=512), 10))
-            comps["leverage_from_sketch_ms"] = max_over_ranks(time_loop(
+            comps["leverage_from_sketch_ms"] = max_over_ranks(time_batch(
                 lambda: approximate_leverage_scores(None, lens, phi, normalize=True, chunk_size=512,
                                                     sketch_rows=sk), 10))
             del cache, sk
         except Exception as ex:
             comps["prepath_error"] = repr(ex)[:200]
+
+        # ---------------- page allocator: host heaps (the reference's design) vs device bitmap ----------------
+        try:
+            from compactor_vllm.kv_cache.page_table import DevicePagedKVCache, PagedKVCache
+            shape = dict(num_layers=32, max_logical_pages_per_head=320, num_pages=4096, page_size=128, H_kv=HKV,
+                         head_dim=8, max_num_batches=4, dtype=torch.bfloat16, device=dev)
+            for name, cls in (("host", PagedKVCache), ("device", DevicePagedKVCache)):
+                c = cls(**shape)
+                s = c.new_batch()
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                reps = 20
+                for i in range(reps):  # a 128-token page per head per call: what a decode step's reserve does
+                    c.reserve_tokens(s, 128)
+                    c.bh_seq_lens[:, s] += 128
+                torch.cuda.synchronize()
+                comps[f"reserve_{name}_us"] = (time.perf_counter() - t0) / reps * 1e6
+                del c
+            c = DevicePagedKVCache(**shape)
+            sl = torch.tensor([c.new_batch()], dtype=torch.int32, device=dev)
+            st = torch.zeros(1, dtype=torch.int32, device=dev)
+            c.reserve_tokens_device(sl, 128, st)
+            comps["reserve_device_nosync_us"] = 1e3 * time_loop(
+                lambda: c.reserve_tokens_device(sl, 1, st), 20)
+            del c
+        except Exception as ex:
+            comps["allocator_error"] = repr(ex)[:200]
 
         # ---------------- decode on the compacted shape ----------------
         flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)

@@ -14,3 +14,9 @@ $DCMD > gpurun_out/plain_decode.log 2>&1 &&
 ncu --set full --clock-control none --import-source on -k regex:decode_attn -s 4 -c 1 -f -o gpurun_out/prof_decode $DCMD > gpurun_out/ncu_decode.log 2>&1
 echo "decode capture rc=$?"
 tail -3 gpurun_out/plain_decode.log gpurun_out/ncu_prefill.log gpurun_out/ncu_decode.log
+RCMD="python tools/probe_rope.py"
+$RCMD > gpurun_out/plain_rope.log 2>&1 &&
+ncu --set full --clock-control none --import-source on -k regex:rope_qk -s 8 -c 1 -f -o gpurun_out/prof_rope $RCMD > gpurun_out/ncu_rope.log 2>&1
+echo "rope capture rc=$?"
+ncu --set full --clock-control none --import-source on -k regex:rope_qk -s 100 -c 1 -f -o gpurun_out/prof_rope_fused $RCMD > gpurun_out/ncu_rope_fused.log 2>&1
+echo "fused rope capture rc=$?"

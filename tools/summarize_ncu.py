@@ -81,3 +81,9 @@ if __name__ == "__main__":
              "algorithmic_bytes": 32768 * (32 + 16) * 128 * 2 + 32768 * 32 * 128 * 2})
     capture(prefix, "prof_decode", "decode_traffic",
             {"command": "ncu --set full --clock-control none -k regex:decode_attn -s 4 -c 1 python tools/prof_decode.py"})
+    capture(prefix, "prof_rope", "rope_traffic",
+            {"command": "ncu --set full --clock-control none -k regex:rope_qk -s 8 -c 1 python tools/probe_rope.py (plain rope, 32768 tokens)",
+             "algorithmic_bytes": 32768 * 40 * 128 * 2 * 2})
+    capture(prefix, "prof_rope_fused", "rope_fused_traffic",
+            {"command": "ncu --set full --clock-control none -k regex:rope_qk -s 100 -c 1 python tools/probe_rope.py (norm + rope + sketch)",
+             "algorithmic_bytes": 32768 * 40 * 128 * 2 * 2 + 32768 * 8 * 96})
