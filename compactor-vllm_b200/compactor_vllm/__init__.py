@@ -1,22 +1,20 @@
 """compactor_vllm — B200-native attention + KV-compression hot path.
 
-Import paths mirror vnchari/compactor-vllm (src/compactor_vllm/__init__.py:1-17)
-for the hot-path surface.  The generation engine (`LLM`: tokenizer, scheduler,
-model runner, HF weight loading) is out of scope for this build — SURVEY.md
-section 8(f) lists it as "next" — so `LLM` raises on construction instead of
-pretending to work.
+Import paths mirror vnchari/compactor-vllm (src/compactor_vllm/__init__.py:7-17).  `LLM` is the
+engine shell of SURVEY 8(f)-3 (core/llm_engine.py): single rank, synthetic weights, CUDA-graph
+decode — it exists to drive the hot path through the reference's top-level call; tokenizer
+download, HF checkpoint loading and multi-process tensor parallelism are outside this build.
 """
 from compactor_vllm.compression import CompressionMethod
 from compactor_vllm.config.engine_config import AttentionBackend, LLMConfig
 from compactor_vllm.config.sampling_params import SamplingParams
 
 
-class LLM:
-    def __init__(self, *args, **kwargs):
-        raise NotImplementedError(
-            "The generation engine is outside this build's scope (attention + KV-compression "
-            "hot path only); drive compactor_vllm.layers.attention.Attention from your runner."
-        )
+def __getattr__(name):  # lazy: importing the package must not need torch.cuda or the native library
+    if name == "LLM":
+        from compactor_vllm.core.llm_engine import LLM
+        return LLM
+    raise AttributeError(name)
 
 
 __all__ = ["LLMConfig", "LLM", "SamplingParams", "AttentionBackend", "CompressionMethod"]

@@ -13,7 +13,7 @@ from typing import Iterable, List, Optional
 import torch
 import torch.distributed as dist
 from compactor_vllm.config.engine_config import LLMConfig
-from compactor_vllm.kv_cache.page_table import KVAllocationStatus, PagedKVCache
+from compactor_vllm.kv_cache.page_table import DevicePagedKVCache, KVAllocationStatus, PagedKVCache
 from torch import nn
 
 logger = logging.getLogger(__name__)
@@ -70,13 +70,14 @@ class KVCacheManager:
             slot = self.seq_id_to_batch.pop(seq_id, None)
             self.paged_cache.free_batch(slot)
 
-    def init_cache(self, model: nn.Module, num_pages: Optional[int] = None):
-        """Size and allocate the cache, then wire it into every attention layer (:67-90)."""
+    def init_cache(self, model: nn.Module, num_pages: Optional[int] = None, device_allocator: bool = False):
+        """Size and allocate the cache, then wire it into every attention layer (:67-90).
+        device_allocator=True: the GPU-resident page allocator (same surface, same page ids)."""
         self.num_pages = (
             int(num_pages) if num_pages is not None
             else self.get_num_pages(self.gpu_frac, self.max_pages_per_batch)
         )
-        self.paged_cache = PagedKVCache(
+        self.paged_cache = (DevicePagedKVCache if device_allocator else PagedKVCache)(
             num_layers=self.num_layers,
             H_kv=self.num_kv_heads,
             head_dim=self.head_dim,
@@ -148,6 +149,8 @@ class KVCacheManager:
 
     @property
     def num_free_pages(self) -> int:
+        if isinstance(self.paged_cache, DevicePagedKVCache):
+            return int(self.paged_cache.free_count.min())
         return min(len(fp) for fp in self.paged_cache.free_pages)
 
     def reclaim_pages(self, seq_ids_to_reclaim: Iterable[int], future_reserved_buffer) -> int:

@@ -115,6 +115,14 @@ class RotaryEmbedding(nn.Module):
         cache = build_cos_sin_cache(rotary_dim, max_position_embeddings, base, rope_scaling)
         self.register_buffer("cos_sin_cache", cache, persistent=False)
 
+    def _apply(self, fn, *args, **kwargs):
+        # `model.to(bfloat16)` must not round the angle table: follow device moves, stay fp32 (the reference
+        # builds its model under the target dtype and computes this buffer in float explicitly, :62-67)
+        cache = self.cos_sin_cache
+        super()._apply(fn, *args, **kwargs)
+        self.cos_sin_cache = cache.to(device=fn(cache).device)
+        return self
+
     def forward(self, positions: torch.Tensor, query: torch.Tensor, key: torch.Tensor):
         q, k, _ = fused_qk_norm_rope(positions, query, key, self.cos_sin_cache, head_size=self.head_size)
         return q, k
