@@ -44,9 +44,15 @@ class ModelRunner:
         self.device = torch.device("cuda", torch.cuda.current_device())
         self.dtype = hf.torch_dtype if isinstance(hf.torch_dtype, torch.dtype) else torch.bfloat16
         kind = "qwen3" if "qwen3" in str(getattr(hf, "model_type", "llama")).lower() else "llama"
-        model = MODEL_REGISTRY[kind](hf)
+        prev = torch.get_default_dtype()
+        torch.set_default_dtype(self.dtype)  # parameters are born in the model dtype on the GPU
+        try:
+            with torch.device(self.device):
+                model = MODEL_REGISTRY[kind](hf)
+        finally:
+            torch.set_default_dtype(prev)
         model.init_synthetic_weights(seed)
-        self.model = model.to(self.dtype).to(self.device).eval()
+        self.model = model.to(self.device).eval()
         self.num_kv_heads = hf.num_key_value_heads
         self.head_dim = getattr(hf, "head_dim", None) or hf.hidden_size // hf.num_attention_heads
         self.kv = KVCacheManager(self.device.index, config)

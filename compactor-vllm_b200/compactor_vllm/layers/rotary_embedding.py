@@ -23,7 +23,7 @@ from compactor_vllm import _native as N
 
 
 def _inverse_frequencies(rotary_dim: int, base: float, rope_scaling: tuple | None) -> torch.Tensor:
-    exponents = torch.arange(0, rotary_dim, 2, dtype=torch.float) / rotary_dim
+    exponents = torch.arange(0, rotary_dim, 2, dtype=torch.float, device="cpu") / rotary_dim
     inv_freq = 1.0 / (base ** exponents)
     if rope_scaling is None:
         return inv_freq
@@ -45,7 +45,9 @@ def build_cos_sin_cache(rotary_dim: int, max_position: int, base: float,
                         rope_scaling: tuple | None = None) -> torch.Tensor:
     """fp32 [max_position, 1, rotary_dim]: cos(t * inv_freq) | sin(t * inv_freq) (reference :62-67)."""
     inv_freq = _inverse_frequencies(rotary_dim, base, rope_scaling)
-    t = torch.arange(max_position, dtype=torch.float)
+    # always on the CPU, whatever the default device: cos / sin differ by an ulp between CPU and CUDA libm and
+    # the table is pinned to the reference modules' CPU-built golden vectors
+    t = torch.arange(max_position, dtype=torch.float, device="cpu")
     freqs = torch.einsum("i,j -> ij", t, inv_freq)
     return torch.cat((freqs.cos(), freqs.sin()), dim=-1).unsqueeze_(1)
 

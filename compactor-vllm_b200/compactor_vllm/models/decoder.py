@@ -153,16 +153,15 @@ class DecoderForCausalLM(nn.Module):
     @torch.no_grad()
     def init_synthetic_weights(self, seed: int = 0) -> None:
         """Random weights of the architecture (no checkpoints without a network): N(0, 0.02) matrices —
-        the HF initializer_range — and norm gains near 1, from one CPU generator so every run and every
-        reference implementation handed the same state dict sees the same numbers."""
-        gen = torch.Generator().manual_seed(seed)
-        for name, p in self.named_parameters():
+        the HF initializer_range — and norm gains near 1, drawn on the parameters' own device (an 8B model is
+        16 GB: not something to generate on the host)."""
+        for i, (name, p) in enumerate(self.named_parameters()):
+            gen = torch.Generator(device=p.device).manual_seed(seed * 100003 + i)
+            val = torch.randn(p.shape, generator=gen, device=p.device, dtype=torch.float32)
             if name.endswith("norm.weight") or name.endswith("layernorm.weight"):
-                val = 1.0 + 0.1 * torch.randn(p.shape, generator=gen)
-            elif name.endswith(".bias"):
-                val = 0.02 * torch.randn(p.shape, generator=gen)
+                val = 1.0 + 0.1 * val
             else:
-                val = 0.02 * torch.randn(p.shape, generator=gen)
+                val = 0.02 * val
             p.copy_(val.to(p.dtype))
 
 
