@@ -32,6 +32,12 @@ _SIGNATURES = {
     "cvllm_pages_init": (_i, [_p, _p, _i, _i, _p]),
     "cvllm_pages_reserve": (_i, [_p, _p, _p, _p, _p, _p, _i, _i, _p, _i, _i, _i, _i, _i, _i, _i, _p, _sz, _p]),
     "cvllm_pages_release": (_i, [_p, _p, _p, _p, _p, _p, _i, _i, _i, _p, _i, _i, _i, _i, _i, _i, _i, _p]),
+    "cvllm_allreduce_flag_bytes": (_sz, []),
+    "cvllm_ipc_alloc": (_i, [_sz, _p, _p]),
+    "cvllm_ipc_open": (_i, [_p, _p]),
+    "cvllm_ipc_close": (_i, [_p]),
+    "cvllm_ipc_free": (_i, [_p]),
+    "cvllm_allreduce_oneshot": (_i, [_p, _i, _i, _p, _i64, _i, _p]),
     "cvllm_rank_scores_workspace_bytes": (_sz, [_i, _i, _i]),
     "cvllm_rank_scores": (_i, [_p, _i64, _p, _i, _i, _i, _i, _p, _p, _sz, _p]),
     "cvllm_store_topk_workspace_bytes": (_sz, [_i, _i, _i, _i]),

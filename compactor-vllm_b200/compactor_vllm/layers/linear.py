@@ -1,0 +1,137 @@
+"""Row-parallel linear + the tensor-parallel all-reduce behind it (reference:
+layers/linear.py:133-153 `RowParallelLinear`: `F.linear` then `dist.all_reduce(y)`).
+
+`PeerAllReduce` is the B200 route for decode-size messages: every rank keeps one cudaIpc-shared staging
+buffer; the row-parallel GEMM writes its partial straight into it (`out=`), and `cvllm_allreduce_oneshot`
+reads all peers' partials over NVLink / NVSwitch and sums them in rank order — one kernel, no ring, identical
+bits on every rank.  Messages above `max_bytes` (prefill) go to NCCL, which is bandwidth-optimal there
+(NVLS in-switch reduction).  The process group only carries the 64-byte IPC handles at start-up.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+import torch.distributed as dist
+import torch.nn.functional as F
+from torch import nn
+
+from compactor_vllm import _native as N
+
+
+class _RawCudaBytes:
+    """`__cuda_array_interface__` view of a raw device pointer, so torch can wrap memory it did not allocate."""
+
+    def __init__(self, ptr: int, nbytes: int):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+
+
+class PeerAllReduce:
+    def __init__(self, group=None, max_bytes: int = 2 << 20, device: Optional[torch.device] = None):
+        assert dist.is_initialized(), "PeerAllReduce needs an initialised process group"
+        self.group = group
+        self.rank = dist.get_rank(group)
+        self.world = dist.get_world_size(group)
+        assert self.world <= 8
+        self.device = device or torch.device("cuda", torch.cuda.current_device())
+        self.max_bytes = int(max_bytes)
+        lib = N.lib()
+        self.flag_bytes = int(lib.cvllm_allreduce_flag_bytes())
+        own = C.c_void_p()
+        handle = C.create_string_buffer(64)
+        with torch.cuda.device(self.device):
+            N.check(lib.cvllm_ipc_alloc(self.max_bytes, C.byref(own), handle), "cvllm_ipc_alloc")
+        handles = [None] * self.world
+        dist.all_gather_object(handles, bytes(handle.raw), group=group)
+        self._own = own.value
+        self._bases = (C.c_void_p * self.world)()
+        for r, h in enumerate(handles):
+            if r == self.rank:
+                self._bases[r] = self._own
+            else:
+                p = C.c_void_p()
+                with torch.cuda.device(self.device):
+                    N.check(lib.cvllm_ipc_open(C.create_string_buffer(h, 64), C.byref(p)), "cvllm_ipc_open")
+                self._bases[r] = p.value
+        raw = torch.as_tensor(_RawCudaBytes(self._own + self.flag_bytes, self.max_bytes), device=self.device)
+        self._payload = raw  # uint8 view of this rank's staging area
+        dist.barrier(group=group)  # every rank has mapped every buffer before the first kernel
+
+    def fits(self, t: torch.Tensor) -> bool:
+        return (t.dtype in (torch.bfloat16, torch.float16) and t.numel() % 8 == 0
+                and t.numel() * t.element_size() <= self.max_bytes)
+
+    def staging(self, shape, dtype) -> torch.Tensor:
+        """A tensor of `shape` living in the shared buffer: let the producer GEMM write into it."""
+        n = 1
+        for s in shape:
+            n *= int(s)
+        nbytes = n * torch.empty((), dtype=dtype).element_size()
+        assert nbytes <= self.max_bytes
+        return self._payload[:nbytes].view(dtype).view(*shape)
+
+    def reduce_staged(self, staged: torch.Tensor) -> torch.Tensor:
+        """Sum over ranks of what each rank put in its staging area (same shape everywhere)."""
+        out = torch.empty(staged.shape, dtype=staged.dtype, device=self.device)
+        rc = N.lib().cvllm_allreduce_oneshot(self._bases, self.rank, self.world, N.ptr(out), staged.numel(),
+                                             N.dtype_code(staged.dtype), N.stream(self.device))
+        N.check(rc, "cvllm_allreduce_oneshot")
+        return out
+
+    def all_reduce(self, t: torch.Tensor) -> torch.Tensor:
+        """Out-of-place sum over ranks; falls to NCCL (in place on a copy-free path) when the message is large."""
+        if not self.fits(t):
+            dist.all_reduce(t, group=self.group)
+            return t
+        st = self.staging(t.shape, t.dtype)
+        st.copy_(t)
+        return self.reduce_staged(st)
+
+    def close(self) -> None:
+        lib = N.lib()
+        torch.cuda.synchronize(self.device)
+        for r in range(self.world):
+            if r != self.rank and self._bases[r]:
+                lib.cvllm_ipc_close(self._bases[r])
+        dist.barrier(group=self.group)
+        lib.cvllm_ipc_free(self._own)
+        self._own = None
+
+
+def shard_rows(full_weight: torch.Tensor, rank: int, world: int) -> torch.Tensor:
+    """Input-dimension shard of a [out, in] weight for tensor-parallel rank `rank` (reference :141-146)."""
+    assert full_weight.shape[1] % world == 0
+    per = full_weight.shape[1] // world
+    return full_weight[:, rank * per:(rank + 1) * per]
+
+
+class RowParallelLinear(nn.Module):
+    """y = all_reduce(x_shard @ W_shard^T (+ bias on rank 0)) — reference layers/linear.py:133-153."""
+
+    def __init__(self, input_size: int, output_size: int, bias: bool = False,
+                 peer_all_reduce: Optional[PeerAllReduce] = None):
+        super().__init__()
+        self.tp_rank = dist.get_rank() if dist.is_initialized() else 0
+        self.tp_size = dist.get_world_size() if dist.is_initialized() else 1
+        assert input_size % self.tp_size == 0
+        self.weight = nn.Parameter(torch.empty(output_size, input_size // self.tp_size))
+        self.bias = nn.Parameter(torch.empty(output_size)) if bias else None
+        self.peer = peer_all_reduce
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        bias = self.bias if self.tp_rank == 0 else None
+        if self.tp_size == 1:
+            return F.linear(x, self.weight, bias)
+        rows = x.reshape(-1, x.shape[-1])
+        out_shape = (*x.shape[:-1], self.weight.shape[0])
+        if self.peer is not None and x.is_cuda and bias is None and self.bias is None:
+            probe = torch.empty(0, dtype=x.dtype)
+            if rows.shape[0] * self.weight.shape[0] * probe.element_size() <= self.peer.max_bytes \
+                    and (rows.shape[0] * self.weight.shape[0]) % 8 == 0 and x.dtype in (torch.bfloat16, torch.float16):
+                st = self.peer.staging((rows.shape[0], self.weight.shape[0]), x.dtype)
+                torch.mm(rows, self.weight.t(), out=st)  # the partial lands in the shared buffer: no copy
+                return self.peer.reduce_staged(st).view(out_shape)
+        y = F.linear(x, self.weight, bias)
+        dist.all_reduce(y)
+        return y

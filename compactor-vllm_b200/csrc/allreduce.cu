@@ -1,0 +1,158 @@
+// One-shot all-reduce over NVLink peer memory for the tensor-parallel o_proj / down_proj outputs of a
+// decode step (reference: layers/linear.py:149-153 `dist.all_reduce` after the row-parallel
+// GEMM).  A decode-size message ([B, hidden] bf16: 16 KB .. 1 MB) is latency-bound: NCCL's ring / tree
+// costs several hops and a proxy wake-up; here every rank reads all peers' buffers directly through
+// NVSwitch (900 GB/s per direction, any-to-any) and sums them in rank order in fp32, so every rank
+// produces the same bits.  Prefill-size messages stay on NCCL (bandwidth-bound, NVLS in-switch reduce).
+//
+// Buffers are cudaMalloc'd here and shared with cudaIpc handles (exchanged by the caller through
+// torch.distributed); layout of a rank's buffer: [ epochs + arrival words | payload ].
+// Barrier per block (a block starts reading as soon as the same block of every peer has arrived): one remote
+// store of a device-side epoch + a spin on local memory; a second one after the reads lets the next call
+// overwrite the payload.  No host-side counters, so a captured call replays unchanged.
+#include <string.h>
+
+#include "common.cuh"
+
+namespace cvllm {
+
+constexpr int kArMaxWorld = 8;
+constexpr int kArBlocks = 64;
+constexpr int kArThreads = 512;
+constexpr size_t kArFlagBytes = (kArBlocks + 2 * kArBlocks * kArMaxWorld) * sizeof(uint32_t) + 256;  // 4.5 KB, payload 256-B aligned
+
+struct ArPeers {
+  void* base[kArMaxWorld];  // base[r] = rank r's buffer as mapped in THIS process
+};
+
+// Flag traffic is volatile (relaxed, system-visible), not release / acquire: a release store at system scope costs
+// a MEMBAR.SYS (~3 us per barrier, measured), and neither barrier needs one — the payload a peer reads after the
+// first barrier was written by an EARLIER kernel of the producer's stream (complete at the kernel boundary and
+// served from the owner's L2, the coherence point for NVLink reads); the second barrier only orders loads that
+// have already returned (their values were consumed before the __syncthreads in front of it).
+__device__ __forceinline__ void st_flag(uint32_t* p, uint32_t v) {
+  asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_flag(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+// Flag words of a rank's buffer: epoch[kArBlocks] | arrive[2 phases][kArBlocks][8].  A block's epoch counts its
+// calls; ranks run the same launches in the same order, so epochs agree without any host-side counter (a CUDA
+// graph replays the same kernel arguments).  Signal = one remote store of the epoch into the peer's word for
+// (phase, block, me); wait = spin on my own words until they reach it.  A peer can be at most one call ahead,
+// hence the >= comparison.
+__device__ __forceinline__ void ar_barrier(const ArPeers& peers, int rank, int world, int phase, uint32_t epoch) {
+  __syncthreads();
+  if (threadIdx.x < world) {
+    const int peer = threadIdx.x;
+    const int word = kArBlocks + (phase * kArBlocks + blockIdx.x) * kArMaxWorld;
+    st_flag(reinterpret_cast<uint32_t*>(peers.base[peer]) + word + rank, epoch);
+    const uint32_t* mine = reinterpret_cast<const uint32_t*>(peers.base[rank]) + word + peer;
+    while ((int32_t)(ld_flag(mine) - epoch) < 0) {}
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ uint4 ld_volatile_v4(const void* p) {
+  uint4 r;
+  asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
+}
+
+template <bool BF16>
+__global__ void __launch_bounds__(kArThreads) allreduce_oneshot_kernel(ArPeers peers, void* __restrict__ out,
+                                                                       int64_t n_vec, int rank, int world) {
+  uint32_t* my_epoch = reinterpret_cast<uint32_t*>(peers.base[rank]) + blockIdx.x;
+  const uint32_t epoch = *my_epoch + 1;
+  ar_barrier(peers, rank, world, 0, epoch);
+  const int64_t stride = (int64_t)gridDim.x * kArThreads;
+  for (int64_t i = (int64_t)blockIdx.x * kArThreads + threadIdx.x; i < n_vec; i += stride) {
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    uint4 v[kArMaxWorld];
+#pragma unroll
+    for (int r = 0; r < kArMaxWorld; ++r)
+      if (r < world) v[r] = ld_volatile_v4(reinterpret_cast<const char*>(peers.base[r]) + kArFlagBytes + i * 16);
+#pragma unroll
+    for (int r = 0; r < kArMaxWorld; ++r) {
+      if (r < world) {  // rank order on every rank: identical bits everywhere
+        const uint32_t w[4] = {v[r].x, v[r].y, v[r].z, v[r].w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float2 f = unpack2<BF16>(w[e]);
+          acc[2 * e] += f.x;
+          acc[2 * e + 1] += f.y;
+        }
+      }
+    }
+    uint4 o;
+    o.x = pack2<BF16>(acc[0], acc[1]); o.y = pack2<BF16>(acc[2], acc[3]);
+    o.z = pack2<BF16>(acc[4], acc[5]); o.w = pack2<BF16>(acc[6], acc[7]);
+    reinterpret_cast<uint4*>(out)[i] = o;
+  }
+  ar_barrier(peers, rank, world, 1, epoch);  // every peer has read my payload: the next call may overwrite it
+  if (threadIdx.x == 0) *my_epoch = epoch;
+}
+
+}  // namespace cvllm
+
+using namespace cvllm;
+
+extern "C" size_t cvllm_allreduce_flag_bytes(void) { return kArFlagBytes; }
+
+// cudaMalloc + zeroed flags + IPC handle (64 bytes written to handle_out_host).  Returns the device pointer.
+extern "C" int cvllm_ipc_alloc(size_t payload_bytes, void** ptr_out_host, void* handle_out_host) {
+  CVLLM_CHECK_ARG(ptr_out_host && handle_out_host && payload_bytes > 0);
+  void* p = nullptr;
+  CVLLM_CHECK_CUDA(cudaMalloc(&p, kArFlagBytes + payload_bytes));
+  CVLLM_CHECK_CUDA(cudaMemset(p, 0, kArFlagBytes));
+  cudaIpcMemHandle_t h;
+  CVLLM_CHECK_CUDA(cudaIpcGetMemHandle(&h, p));
+  memcpy(handle_out_host, &h, sizeof(h));
+  CVLLM_CHECK_CUDA(cudaDeviceSynchronize());
+  *ptr_out_host = p;
+  return CVLLM_OK;
+}
+
+extern "C" int cvllm_ipc_open(const void* handle_host, void** ptr_out_host) {
+  CVLLM_CHECK_ARG(handle_host && ptr_out_host);
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle_host, sizeof(h));
+  CVLLM_CHECK_CUDA(cudaIpcOpenMemHandle(ptr_out_host, h, cudaIpcMemLazyEnablePeerAccess));
+  return CVLLM_OK;
+}
+
+extern "C" int cvllm_ipc_close(void* peer_ptr) {
+  CVLLM_CHECK_CUDA(cudaIpcCloseMemHandle(peer_ptr));
+  return CVLLM_OK;
+}
+
+extern "C" int cvllm_ipc_free(void* own_ptr) {
+  CVLLM_CHECK_CUDA(cudaFree(own_ptr));
+  return CVLLM_OK;
+}
+
+// out[i] = sum_r payload_r[i], i < numel (16-bit elements, numel % 8 == 0).  peer_bases_host[r] = rank r's buffer
+// as mapped in this process (own buffer for r == rank).  Every rank must launch with the same numel.
+extern "C" int cvllm_allreduce_oneshot(void* const* peer_bases_host, int rank, int world, void* out, int64_t numel,
+                                       int dtype, cvllm_stream_t stream) {
+  CVLLM_CHECK_ARG(peer_bases_host && out && world >= 1 && world <= kArMaxWorld && rank >= 0 && rank < world);
+  CVLLM_CHECK_ARG(numel >= 0 && numel % 8 == 0);
+  CVLLM_CHECK_ARG(dtype == CVLLM_F16 || dtype == CVLLM_BF16);
+  CVLLM_CHECK_ALIGN(aligned16(out));
+  if (numel == 0) return CVLLM_OK;
+  ArPeers peers;
+  for (int r = 0; r < kArMaxWorld; ++r) peers.base[r] = r < world ? peer_bases_host[r] : nullptr;
+  const int64_t n_vec = numel / 8;
+  int blocks = (int)((n_vec + kArThreads - 1) / kArThreads);
+  blocks = blocks < 1 ? 1 : (blocks > kArBlocks ? kArBlocks : blocks);
+  auto st = static_cast<cudaStream_t>(stream);
+  if (dtype == CVLLM_BF16)
+    allreduce_oneshot_kernel<true><<<blocks, kArThreads, 0, st>>>(peers, out, n_vec, rank, world);
+  else
+    allreduce_oneshot_kernel<false><<<blocks, kArThreads, 0, st>>>(peers, out, n_vec, rank, world);
+  CVLLM_CHECK_LAUNCH();
+  return CVLLM_OK;
+}

@@ -123,6 +123,28 @@ int cvllm_pages_release(uint32_t* free_bits, int32_t* free_count, const int32_t*
                         int reserved_batch, cvllm_stream_t stream);
 
 /* ------------------------------------------------------------------------
+ * The step after the path: the tensor-parallel all-reduce
+ * behind o_proj / down_proj — layers/linear.py:149-153 `dist.all_reduce(y)`.
+ * One-shot all-reduce over NVLink peer memory for decode-size messages;
+ * every rank reads all peers' buffers and sums in rank order (fp32), so all
+ * ranks hold identical bits.  Buffers come from cvllm_ipc_alloc (cudaMalloc +
+ * cudaIpc handle, flags zeroed); the 64-byte handles are exchanged by the
+ * caller (torch.distributed) and opened with cvllm_ipc_open.  A rank's payload
+ * starts cvllm_allreduce_flag_bytes() into its buffer.  *_host = host pointers.
+ * --------------------------------------------------------------------- */
+size_t cvllm_allreduce_flag_bytes(void);
+int cvllm_ipc_alloc(size_t payload_bytes, void** ptr_out_host, void* handle_out_host);
+int cvllm_ipc_open(const void* handle_host, void** ptr_out_host);
+int cvllm_ipc_close(void* peer_ptr);
+int cvllm_ipc_free(void* own_ptr);
+/* out[i] = sum over ranks of payload_r[i]; numel 16-bit elements, % 8 == 0,
+ * the same on every rank; world <= 8.  peer_bases_host[r] = rank r's buffer as
+ * mapped in this process.  The payload may be rewritten as soon as the kernel
+ * has finished on this rank's stream. */
+int cvllm_allreduce_oneshot(void* const* peer_bases_host, int rank, int world, void* out,
+                            int64_t numel, int dtype, cvllm_stream_t stream);
+
+/* ------------------------------------------------------------------------
  * Selection + compaction
  * --------------------------------------------------------------------- */
 

@@ -95,3 +95,33 @@ def test_kv_head_shard_partitions_heads():
         assert got[-1][1] == hkv and got[-1][3] == hq
         with pytest.raises(AssertionError):
             A.kv_head_shard(0, 3, hq, hkv)
+
+
+def _row_parallel_worker(rank: int, world: int, port: int, out_dir: str):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from compactor_vllm.layers.linear import RowParallelLinear, shard_rows
+
+        g = torch.Generator().manual_seed(3)  # the same full weight / input on every rank
+        W = torch.randn((24, 16), generator=g)
+        bias = torch.randn(24, generator=g)
+        x = torch.randn((5, 16), generator=g)
+        lin = RowParallelLinear(16, 24, bias=True)  # no peer buffer: torch.distributed carries the reduce
+        assert lin.tp_size == world and lin.weight.shape == (24, 16 // world)
+        with torch.no_grad():
+            lin.weight.copy_(shard_rows(W, rank, world))
+            lin.bias.copy_(bias)
+            per = 16 // world
+            y = lin(x[:, rank * per:(rank + 1) * per])
+        want = x @ W.t() + bias  # the bias is added on rank 0 only (reference layers/linear.py:149)
+        assert torch.allclose(y, want, atol=1e-5), (y - want).abs().max()
+        Path(out_dir, f"rp{rank}").write_text("ok")
+    finally:
+        dist.destroy_process_group()
+
+
+def test_row_parallel_linear_two_rank_gloo(tmp_path):
+    world = 2
+    mp.spawn(_row_parallel_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    assert all((tmp_path / f"rp{r}").exists() for r in range(world))

@@ -1,0 +1,156 @@
+"""Multi-GPU check + timing of the one-shot peer all-reduce.  One process per GPU:
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 \
+        tools/tp_allreduce_check.py
+
+Parity: against NCCL `all_reduce` of the same partials (fp32 reference = sum of the bf16 partials in fp32,
+rounded once), identical bits on every rank, through `RowParallelLinear` with a sharded weight against the
+unsharded GEMM, and replayed from a CUDA graph.  Timing: CUDA events, max over ranks, decode-size messages
+([B, 8192] bf16, Llama-3.1-70B hidden) and the config-5 prefill message on NCCL for context.  Rank 0 prints JSON."""
+import json
+import os
+import sys
+from pathlib import Path
+
+import torch
+import torch.distributed as dist
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path[:0] = [str(ROOT), str(ROOT / "compactor-vllm_b200")]
+
+
+def timed(fn, iters=50):
+    for _ in range(5):
+        fn()
+    dist.barrier()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(iters):
+        fn()
+    b.record()
+    b.synchronize()
+    t = torch.tensor([a.elapsed_time(b) / iters], device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t) * 1e3  # us
+
+
+def main():
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)))
+    dev = torch.device("cuda", torch.cuda.current_device())
+    dist.init_process_group("nccl", device_id=dev)
+    from compactor_vllm.layers.linear import PeerAllReduce, RowParallelLinear, shard_rows
+
+    par = PeerAllReduce(max_bytes=4 << 20)
+    res = {"world": world, "checks": {}, "us": {}}
+    g = torch.Generator(device=dev).manual_seed(100 + rank)
+    ok = True
+    for rows in (1, 16, 64, 256):
+        x = torch.randn((rows, 8192), generator=g, device=dev).bfloat16()
+        got = par.all_reduce(x.clone())
+        # fp32 reference: gather all partials, sum in rank order, round once
+        parts = [torch.empty_like(x) for _ in range(world)]
+        dist.all_gather(parts, x)
+        want = torch.stack([p.float() for p in parts]).sum(0)
+        # the kernel accumulates in fp32 in rank order: same arithmetic
+        acc = torch.zeros_like(want)
+        for p in parts:
+            acc += p.float()
+        exact = torch.equal(got, acc.bfloat16())
+        same = [torch.empty_like(got) for _ in range(world)]
+        dist.all_gather(same, got)
+        identical = all(torch.equal(same[0], s) for s in same)
+        nccl = x.clone()
+        dist.all_reduce(nccl)
+        close = (got.float() - want).abs().max().item() <= 2e-2 * want.abs().max().item()
+        near_nccl = (got.float() - nccl.float()).abs().max().item() <= 4e-2 * want.abs().max().item()
+        res["checks"][f"rows{rows}"] = {"bit_exact_vs_fp32_rank_order": exact, "identical_on_all_ranks": identical,
+                                        "close_to_fp32": close, "close_to_nccl": near_nccl}
+        ok &= exact and identical and close and near_nccl
+        xs = x.clone()
+        res["us"][f"peer_{rows}x8192"] = timed(lambda: par.all_reduce(xs))
+        xn = x.clone()
+        res["us"][f"nccl_{rows}x8192"] = timed(lambda: dist.all_reduce(xn))
+
+    # RowParallelLinear: sharded weight + peer all-reduce == unsharded GEMM (bf16 tolerance)
+    gw = torch.Generator(device=dev).manual_seed(7)  # same seed on every rank: the full weight
+    W = (0.02 * torch.randn((8192, 8192), generator=gw, device=dev)).bfloat16()
+    xin = torch.randn((16, 8192), generator=gw, device=dev).bfloat16()
+    lin = RowParallelLinear(8192, 8192, peer_all_reduce=par).to(dev).to(torch.bfloat16)
+    with torch.no_grad():
+        lin.weight.copy_(shard_rows(W, rank, world))
+        per = 8192 // world
+        y = lin(xin[:, rank * per:(rank + 1) * per].contiguous())
+        full = xin.float() @ W.float().t()
+        rel = ((y.float() - full).norm() / full.norm()).item()
+    res["checks"]["row_parallel_rel_err"] = rel
+    ok &= rel < 2e-2
+
+    # CUDA graph replay of GEMM -> staging -> one-shot all-reduce (the decode step's shape of use)
+    with torch.no_grad():
+        xs = xin[:, rank * per:(rank + 1) * per].contiguous()
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            lin(xs)
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph, stream=side):
+                yg = lin(xs)
+        torch.cuda.current_stream().wait_stream(side)
+        dist.barrier()
+        for _ in range(3):
+            graph.replay()
+        torch.cuda.synchronize()
+        res["checks"]["graph_replay_equals_eager"] = bool(torch.equal(yg, y))
+        ok &= res["checks"]["graph_replay_equals_eager"]
+        res["us"]["graph_gemm_plus_peer_allreduce_16x8192"] = timed(graph.replay)
+        lin_nccl = RowParallelLinear(8192, 8192).to(dev).to(torch.bfloat16)
+        lin_nccl.weight.copy_(shard_rows(W, rank, world))
+        res["us"]["eager_gemm_plus_nccl_allreduce_16x8192"] = timed(lambda: lin_nccl(xs))
+
+    # like for like: both routes replayed from CUDA graphs (no Python launch path), 8 calls per replay
+    def graphed(fn, reps=8):
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            fn()
+            gr = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gr, stream=side):
+                for _ in range(reps):
+                    fn()
+        torch.cuda.current_stream().wait_stream(side)
+        dist.barrier()
+        return timed(gr.replay) / reps
+
+    with torch.no_grad():
+        for rows in (1, 16, 64, 128):
+            st = par.staging((rows, 8192), torch.bfloat16)
+            st.normal_()
+            res["us"][f"graph_peer_allreduce_{rows}x8192"] = graphed(lambda: par.reduce_staged(st))
+            xn = torch.randn((rows, 8192), device=dev).bfloat16()
+            try:
+                res["us"][f"graph_nccl_allreduce_{rows}x8192"] = graphed(lambda: dist.all_reduce(xn))
+            except Exception as ex:
+                res["us"][f"graph_nccl_allreduce_{rows}x8192"] = repr(ex)[:80]
+        res["us"]["graph_gemm_peer_16x8192"] = graphed(lambda: lin(xs))
+        try:
+            res["us"]["graph_gemm_nccl_16x8192"] = graphed(lambda: lin_nccl(xs))
+        except Exception as ex:
+            res["us"]["graph_gemm_nccl_16x8192"] = repr(ex)[:80]
+
+    # config 5's prefill message on NCCL, for context ([32768, 8192] bf16 = 512 MiB)
+    big = torch.randn((32768, 8192), device=dev).bfloat16()
+    us = timed(lambda: dist.all_reduce(big), iters=5)
+    res["us"]["nccl_32768x8192"] = us
+    res["nccl_prefill_busbw_gbs"] = big.numel() * 2 * 2 * (world - 1) / world / (us * 1e-6) / 1e9
+    res["ok"] = bool(ok)
+    par.close()
+    if rank == 0:
+        print(json.dumps(res))
+    dist.destroy_process_group()
+    sys.exit(0 if ok else 1)
+
+
+if __name__ == "__main__":
+    main()
