@@ -73,7 +73,8 @@ def make_inputs(n_tok: int, device, dtype, seed: int):
     coef = torch.randn((n_tok, HKV, 12), generator=g, device=device) * torch.linspace(2.0, 0.2, 12, device=device)
     pos = torch.linspace(0, 50.0, n_tok, device=device)[:, None, None]
     low = torch.einsum("nhr,hrd->nhd", coef, basis) + 0.5 * torch.sin(pos + torch.arange(D, device=device) * 0.1)
-    k_pre = (low + 0.3 * torch.randn((n_tok, HKV, D), generator=g, device=device)).to(dtype)
+    # .contiguous(): einsum hands back a head-major layout; the engine's pre-RoPE keys are token-major [N, HKV, D]
+    k_pre = (low + 0.3 * torch.randn((n_tok, HKV, D), generator=g, device=device)).to(dtype).contiguous()
     qkv = qkv.to(dtype)
     kview = qkv[:, HQ * D:(HQ + HKV) * D].view(n_tok, HKV, D)
     kview.add_((0.25 * low).to(dtype))
@@ -487,22 +488,39 @@ def main():
     # ---------------- headline: K timed steps ----------------
     for _ in range(args.warmup):
         w.prefill_step()
-    barrier()
-    w.attn_events.clear()
-    sampler = ClockSampler(local)
-    barrier()
-    sampler.start()
-    launches0 = lib.cvllm_launch_count()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    ev0.record()
-    for _ in range(args.steps):
-        w.prefill_step()
-    ev1.record()
-    barrier()
-    launches = lib.cvllm_launch_count() - launches0
-    ms_step = max_over_ranks(ev0.elapsed_time(ev1) / args.steps)
-    attn_ms = sum(s.elapsed_time(e) for s, e in w.attn_events) / max(1, len(w.attn_events))
-    clocks = sampler.stop()
+    def timed_block():
+        barrier()
+        w.attn_events.clear()
+        sampler = ClockSampler(local)
+        barrier()
+        sampler.start()
+        launches0 = lib.cvllm_launch_count()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
+        marks = []
+        for _ in range(args.steps):
+            w.prefill_step()
+            marks.append(torch.cuda.Event(enable_timing=True))
+            marks[-1].record()
+        ev1.record()
+        barrier()
+        n_launch = lib.cvllm_launch_count() - launches0
+        ms = max_over_ranks(ev0.elapsed_time(ev1) / args.steps)
+        steps_sorted = sorted(a.elapsed_time(b) for a, b in zip([ev0] + marks[:-1], marks))
+        a_ms = sum(s.elapsed_time(e) for s, e in w.attn_events) / max(1, len(w.attn_events))
+        return ms, steps_sorted, a_ms, n_launch, sampler.stop()
+
+    ms_step, per_step, attn_ms, launches, clocks = timed_block()
+    # The timing rules' "rejected and re-measured once": a block that saw a thermal / hw slowdown, or whose
+    # mean step is far above its own median step (a stall outside the kernels: another process on the box,
+    # a driver hiccup), is measured once more; the second block is the one reported, the first is kept on the line.
+    remeasured = None
+    bad_reasons = {"hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown"} & set(clocks.get("reasons") or [])
+    stalled = max_over_ranks(1.0 if ms_step > 1.25 * per_step[len(per_step) // 2] else 0.0) > 0
+    if max_over_ranks(1.0 if bad_reasons else 0.0) > 0 or stalled:  # the same decision on every rank
+        remeasured = {"first_ms_per_step": ms_step, "first_clocks": clocks,
+                      "why": sorted(bad_reasons) or "mean step > 1.25 x median step"}
+        ms_step, per_step, attn_ms, launches, clocks = timed_block()
     value = flops * world / (ms_step * 1e-3) / 1e12
     total_launches = int(sum_over_ranks(float(launches)))
 
@@ -511,6 +529,8 @@ def main():
     kept_pairs = int(kept_bh.sum())
 
     comps = {"prefill_tflops_with_compression": value, "prefill_attn_kernel_ms": attn_ms,
+             "step_ms_min_med_max": [per_step[0], per_step[len(per_step) // 2], per_step[-1]],
+             **({"remeasured": remeasured} if remeasured else {}),
              "kept_pairs": kept_pairs, "retain_budget": w.retain}
     roof_dec = None
     e2e = None
@@ -660,10 +680,59 @@ def main():
             e2e_step()
         barrier()
         e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3 / n_e2e)
-        e2e = {"value": flops * world / (e2e_ms * 1e-3) / 1e12, "unit": "TFLOP/s",
+        # The same call, software-pipelined the way a serving loop feeds it: two device input buffers and two
+        # pinned output buffers; the H2D of step i+1 (copy stream) and the D2H of step i-1 (second copy stream)
+        # run under step i's kernels.  Every step still moves its own inputs from pinned host memory and lands
+        # its own output in pinned host memory inside the timed region; a host output buffer is reused only
+        # after its previous D2H has completed (the host-side read).
+        d_in = [(d_qkv, d_kpre), (torch.empty_like(w.qkv), torch.empty_like(w.k_pre))]
+        h_outs = [h_out, torch.empty((n_tok, HQ, D), dtype=w.dtype).pin_memory()]
+        s_in, s_out = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+        ev_in = [torch.cuda.Event() for _ in range(2)]
+        ev_done = [torch.cuda.Event() for _ in range(2)]
+        ev_out = [torch.cuda.Event() for _ in range(2)]
+
+        def e2e_pipelined(n_steps):
+            main = torch.cuda.current_stream()
+            for ev in ev_done + ev_out:
+                ev.record(main)
+            for i in range(n_steps):
+                bsel = i & 1
+                dq, dk = d_in[bsel]
+                with torch.cuda.stream(s_in):
+                    s_in.wait_event(ev_done[bsel])  # step i-2 has finished reading this input buffer
+                    dk.copy_(h_kpre, non_blocking=True)
+                    dq.copy_(h_qkv, non_blocking=True)
+                    ev_in[bsel].record(s_in)
+                main.wait_event(ev_in[bsel])
+                q, k, v = split_qkv(dq)
+                out = w.prefill_step(q, k, v, dk)
+                ev_done[bsel].record(main)
+                ev_out[bsel].synchronize()  # the host has step i-2's output: its buffer may be rewritten
+                with torch.cuda.stream(s_out):
+                    s_out.wait_event(ev_done[bsel])
+                    h_outs[bsel].copy_(out, non_blocking=True)
+                    out.record_stream(s_out)
+                    ev_out[bsel].record(s_out)
+            for ev in ev_out:
+                ev.synchronize()
+            main.synchronize()
+
+        e2e_pipelined(3)
+        barrier()
+        t0 = time.perf_counter()
+        e2e_pipelined(2 * n_e2e)
+        barrier()
+        pipe_ms = max_over_ranks((time.perf_counter() - t0) * 1e3 / (2 * n_e2e))
+        e2e = {"value": flops * world / (pipe_ms * 1e-3) / 1e12, "unit": "TFLOP/s",
                "h2d_bytes_per_step": int(h_qkv.numel() * 2 + h_kpre.numel() * 2),
-               "d2h_bytes_per_step": int(h_out.numel() * 2), "ms_per_step": e2e_ms,
+               "d2h_bytes_per_step": int(h_out.numel() * 2), "ms_per_step": pipe_ms,
+               "mode": "double-buffered: step i+1's H2D and step i-1's D2H overlap step i's kernels; "
+                       "every step copies its own inputs from pinned host memory and its output to pinned host "
+                       "memory inside the timed region (host wall clock, first H2D to last D2H)",
+               "serial_value": flops * world / (e2e_ms * 1e-3) / 1e12, "serial_ms_per_step": e2e_ms,
                "api": "CompactorCompression.pre/post_rope_scoring + Attention.forward, pinned host q/k/v in, out back"}
+        del d_in, h_outs
         del h_qkv, h_kpre, h_out, d_qkv, d_kpre
 
         # ---------------- CPU baseline (rank 0, N=1 only) ----------------
