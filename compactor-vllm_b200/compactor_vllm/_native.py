@@ -32,6 +32,7 @@ _SIGNATURES = {
     "cvllm_pages_init": (_i, [_p, _p, _i, _i, _p]),
     "cvllm_pages_reserve": (_i, [_p, _p, _p, _p, _p, _p, _i, _i, _p, _i, _i, _i, _i, _i, _i, _i, _p, _sz, _p]),
     "cvllm_pages_release": (_i, [_p, _p, _p, _p, _p, _p, _i, _i, _i, _p, _i, _i, _i, _i, _i, _i, _i, _p]),
+    "cvllm_debug_decode_trace": (_i, [_p]),
     "cvllm_allreduce_flag_bytes": (_sz, []),
     "cvllm_ipc_alloc": (_i, [_sz, _p, _p]),
     "cvllm_ipc_open": (_i, [_p, _p]),

@@ -54,7 +54,22 @@ struct DecodeParams {
   int lens_by_slot;   // seq_lens_bh is the cache's [Bmax+1, HKV] table, indexed through batch_mapping
   int mode;           // 0 = normal; 1 = consumers only drain the ring (load ceiling, profiling only)
   float scale_log2;
+#ifdef CVLLM_DECODE_TRACE
+  unsigned long long* trace;  // profiling build only (tools/trace_decode.py): 8 globaltimer stamps per CTA
+#endif
 };
+
+__device__ __forceinline__ unsigned long long gtime() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+// The stamps cost ~2 us at B = 1 (measured), so they exist only in the -DCVLLM_DECODE_TRACE variant build.
+#ifdef CVLLM_DECODE_TRACE
+#define DEC_TRACE(slot) do { if (p.trace) p.trace[blockIdx.x * 8 + (slot)] = gtime(); } while (0)
+#else
+#define DEC_TRACE(slot) do { } while (0)
+#endif
 
 // One warp's 16-key slice: K rows r / r+8 (4 chunks each), V for 4 keys x 2 chunks.
 struct Slice {
@@ -116,6 +131,7 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_consta
     return p.seq_lens_bh[p.batch_mapping[b] * p.HKV + (i - b * p.HKV)];
   };
 
+  if (tid == 0) DEC_TRACE(0);
   if (tid == kDecCons) {  // producer warp: descriptor fetch overlaps the prologue
     tma_prefetch_desc(&tm_k);
     tma_prefetch_desc(&tm_v);
@@ -153,6 +169,7 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_consta
     __syncthreads();
   }
   const int U = s_prefix[BH];
+  if (tid == 0) DEC_TRACE(1);
 
   // zero rows for empty heads (reference leaves them uninitialised)
   for (int i = c; i < BH; i += C) {
@@ -286,6 +303,7 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_consta
 
       // every warp waits (so nobody can run a full ring ahead) and releases the slots
       mbar_wait(&bar_full[ks_slot], k_par);
+      if (tid == 0 && u == u_begin && uu == ua) DEC_TRACE(2);
       if (n_valid > 0 && p.mode == 0) {
         Slice cur;
 #pragma unroll
@@ -371,6 +389,7 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_consta
       if (lane == 0) mbar_arrive(&bar_empty[vs_slot]);
     }
 
+    if (tid == 0) DEC_TRACE(3);
     // ---- per-warp state -> smem ----
 #pragma unroll
     for (int o = 4; o < 32; o <<= 1) {
@@ -447,6 +466,7 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_consta
         s_last = (done == h_end - h_beg);
       }
       cons_bar();
+      if (tid == 0) DEC_TRACE(6);
       if (s_last) {
         __threadfence();
         const int c_first = (int)((((int64_t)h_beg + 1) * C - 1) / U);
@@ -496,6 +516,7 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_consta
           }
         }
         cons_bar();
+        if (tid == 0) DEC_TRACE(7);
         fold_warps();
         cons_bar();
         write_out();
@@ -503,6 +524,12 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_consta
       }
     }
     cons_bar();  // s_merge / s_final reused by the next segment
+#ifdef CVLLM_DECODE_TRACE
+    if (tid == 0 && p.trace) {
+      DEC_TRACE(4);
+      p.trace[blockIdx.x * 8 + 5] = (unsigned long long)(whole ? 0 : (s_last ? 2 : 1));
+    }
+#endif
     u = seg_end;
   }
 }
@@ -510,6 +537,18 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_consta
 }  // namespace cvllm
 
 using namespace cvllm;
+
+static unsigned long long* g_decode_trace = nullptr;
+// profiling only: device buffer of 8 x #CTAs uint64 that the next decode launches stamp (nullptr: off).
+// Returns 0 when the library was built with -DCVLLM_DECODE_TRACE, -1 when the stamps are compiled out.
+extern "C" int cvllm_debug_decode_trace(void* dev_buf) {
+  g_decode_trace = reinterpret_cast<unsigned long long*>(dev_buf);
+#ifdef CVLLM_DECODE_TRACE
+  return 0;
+#else
+  return -1;
+#endif
+}
 
 static int decode_ctas(int num_ctas) { return num_ctas > 0 ? num_ctas : sm_count(); }
 static size_t decode_counter_bytes(size_t BH) { return (BH * 4 + 255) & ~(size_t)255; }
@@ -555,6 +594,9 @@ static int launch_decode_attn(const void* q, void* out, const void* k_cache, con
   p.box_rows = PS < kUnit ? PS : kUnit;
   p.lens_by_slot = lens_by_slot;
   p.scale_log2 = sm_scale * 1.4426950408889634f;
+#ifdef CVLLM_DECODE_TRACE
+  p.trace = g_decode_trace;
+#endif
   {
     static const int mode = [] { const char* e = getenv("CVLLM_DECODE_MODE"); return e ? atoi(e) : 0; }();
     p.mode = mode;

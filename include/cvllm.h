@@ -50,6 +50,10 @@ const char* cvllm_last_error(void);
 /* Number of kernels this library has launched in this process (monotonic).
  * Lets a caller report how many of its kernels ran inside a timed region. */
 uint64_t cvllm_launch_count(void);
+/* Profiling only: in a library built with -DCVLLM_DECODE_TRACE (tools/trace_decode.py) the next decode launches
+ * stamp 8 globaltimer values per CTA (entry, lengths read, first unit landed, streaming done, merge done, role,
+ * ticket taken, slots folded) into dev_buf (8 * #CTAs uint64); NULL = off.  Returns -1 in the normal build. */
+int cvllm_debug_decode_trace(void* dev_buf);
 
 /* ------------------------------------------------------------------------
  * Store path
