@@ -28,20 +28,32 @@ class _RawCudaBytes:
 
 
 class PeerAllReduce:
-    def __init__(self, group=None, max_bytes: int = 2 << 20, device: Optional[torch.device] = None):
+    def __init__(self, group=None, max_bytes: Optional[int] = None, device: Optional[torch.device] = None,
+                 twoshot_min_bytes: Optional[int] = None):
         assert dist.is_initialized(), "PeerAllReduce needs an initialised process group"
         self.group = group
         self.rank = dist.get_rank(group)
         self.world = dist.get_world_size(group)
         assert self.world <= 8
         self.device = device or torch.device("cuda", torch.cuda.current_device())
+        # One-shot reads (world-1) x message per rank, two-shot 2 x (world-1)/world x message plus one publishing
+        # barrier (a system-scope fence): measured switch points on one 8 x B200 box (profiles/r01h_tp_allreduce_n8.json).
+        # 8 ranks: two-shot wins from ~3 MB (4 MB: 35.6 us vs 54.2 one-shot / 56.1 NCCL; 8 MB: 59 vs 73 NCCL) but
+        # its publishing fence costs ~17 us, so small messages stay one-shot (7.8 us at 16 KB vs 24.3);
+        # 2-4 ranks: the one-shot form is never slower up to 8 MB, where it meets NCCL.
+        if max_bytes is None:
+            max_bytes = 8 << 20
+        if twoshot_min_bytes is None:
+            twoshot_min_bytes = (3 << 20) if self.world >= 8 else (4 << 20) if self.world >= 6 else (1 << 62)
         self.max_bytes = int(max_bytes)
+        self.twoshot_min_bytes = int(twoshot_min_bytes)
         lib = N.lib()
         self.flag_bytes = int(lib.cvllm_allreduce_flag_bytes())
         own = C.c_void_p()
         handle = C.create_string_buffer(64)
         with torch.cuda.device(self.device):
-            N.check(lib.cvllm_ipc_alloc(self.max_bytes, C.byref(own), handle), "cvllm_ipc_alloc")
+            # payload area + result area of the two-shot form
+            N.check(lib.cvllm_ipc_alloc(2 * self.max_bytes, C.byref(own), handle), "cvllm_ipc_alloc")
         handles = [None] * self.world
         dist.all_gather_object(handles, bytes(handle.raw), group=group)
         self._own = own.value
@@ -74,6 +86,11 @@ class PeerAllReduce:
     def reduce_staged(self, staged: torch.Tensor) -> torch.Tensor:
         """Sum over ranks of what each rank put in its staging area (same shape everywhere)."""
         out = torch.empty(staged.shape, dtype=staged.dtype, device=self.device)
+        if staged.numel() * staged.element_size() >= self.twoshot_min_bytes:
+            rc = N.lib().cvllm_allreduce_twoshot(self._bases, self.rank, self.world, N.ptr(out), staged.numel(),
+                                                 N.dtype_code(staged.dtype), self.max_bytes, N.stream(self.device))
+            N.check(rc, "cvllm_allreduce_twoshot")
+            return out
         rc = N.lib().cvllm_allreduce_oneshot(self._bases, self.rank, self.world, N.ptr(out), staged.numel(),
                                              N.dtype_code(staged.dtype), N.stream(self.device))
         N.check(rc, "cvllm_allreduce_oneshot")

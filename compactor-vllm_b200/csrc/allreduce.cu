@@ -19,7 +19,8 @@ namespace cvllm {
 constexpr int kArMaxWorld = 8;
 constexpr int kArBlocks = 64;
 constexpr int kArThreads = 512;
-constexpr size_t kArFlagBytes = (kArBlocks + 2 * kArBlocks * kArMaxWorld) * sizeof(uint32_t) + 256;  // 4.5 KB, payload 256-B aligned
+constexpr int kArPhases = 3;  // one-shot uses phases 0-1, two-shot 0-2
+constexpr size_t kArFlagBytes = (kArBlocks + kArPhases * kArBlocks * kArMaxWorld) * sizeof(uint32_t) + 256;  // 6.5 KB, payload 256-B aligned
 
 struct ArPeers {
   void* base[kArMaxWorld];  // base[r] = rank r's buffer as mapped in THIS process
@@ -39,19 +40,31 @@ __device__ __forceinline__ uint32_t ld_flag(const uint32_t* p) {
   return v;
 }
 
-// Flag words of a rank's buffer: epoch[kArBlocks] | arrive[2 phases][kArBlocks][8].  A block's epoch counts its
+// Flag words of a rank's buffer: epoch[kArBlocks] | arrive[kArPhases][kArBlocks][8].  A block's epoch counts its
 // calls; ranks run the same launches in the same order, so epochs agree without any host-side counter (a CUDA
 // graph replays the same kernel arguments).  Signal = one remote store of the epoch into the peer's word for
 // (phase, block, me); wait = spin on my own words until they reach it.  A peer can be at most one call ahead,
 // hence the >= comparison.
+// PUBLISH = true: data written by THIS kernel (by any thread of the block, before the leading __syncthreads) must be
+// visible to the peers that see the flag — a system-scope fence in front of the flag store (cumulative over the
+// block's writes through the barrier) and an acquire load on the polling side.
+template <bool PUBLISH = false>
 __device__ __forceinline__ void ar_barrier(const ArPeers& peers, int rank, int world, int phase, uint32_t epoch) {
   __syncthreads();
   if (threadIdx.x < world) {
     const int peer = threadIdx.x;
     const int word = kArBlocks + (phase * kArBlocks + blockIdx.x) * kArMaxWorld;
+    if (PUBLISH) __threadfence_system();
     st_flag(reinterpret_cast<uint32_t*>(peers.base[peer]) + word + rank, epoch);
     const uint32_t* mine = reinterpret_cast<const uint32_t*>(peers.base[rank]) + word + peer;
-    while ((int32_t)(ld_flag(mine) - epoch) < 0) {}
+    if (PUBLISH) {
+      uint32_t v;
+      do {
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(mine) : "memory");
+      } while ((int32_t)(v - epoch) < 0);
+    } else {
+      while ((int32_t)(ld_flag(mine) - epoch) < 0) {}
+    }
   }
   __syncthreads();
 }
@@ -93,6 +106,58 @@ __global__ void __launch_bounds__(kArThreads) allreduce_oneshot_kernel(ArPeers p
     reinterpret_cast<uint4*>(out)[i] = o;
   }
   ar_barrier(peers, rank, world, 1, epoch);  // every peer has read my payload: the next call may overwrite it
+  if (threadIdx.x == 0) *my_epoch = epoch;
+}
+
+// Two-shot: rank r reduces slice r of the message (reads 1/world of every peer's payload), leaves it in the RESULT
+// area of its own buffer, and after a publishing barrier every rank gathers the world slices from their owners.
+// Per rank it moves 2 x (world-1)/world x message over NVLink instead of the one-shot's (world-1) x message: the
+// form for messages of a few MB at 4-8 ranks.  Same rank-order fp32 sum, so the bits equal the one-shot's.
+// Block b works on the same sub-range of every slice on every rank, so the per-block barriers suffice.
+template <bool BF16>
+__global__ void __launch_bounds__(kArThreads) allreduce_twoshot_kernel(ArPeers peers, void* __restrict__ out,
+                                                                       int64_t n_vec, int64_t result_off, int rank,
+                                                                       int world) {
+  uint32_t* my_epoch = reinterpret_cast<uint32_t*>(peers.base[rank]) + blockIdx.x;
+  const uint32_t epoch = *my_epoch + 1;
+  const int64_t slice = (n_vec + world - 1) / world;
+  const int64_t stride = (int64_t)gridDim.x * kArThreads;
+  ar_barrier(peers, rank, world, 0, epoch);  // every peer's payload is there (written by earlier kernels)
+  {
+    const int64_t lo = rank * slice, hi = min(n_vec, lo + slice);
+    uint4* res = reinterpret_cast<uint4*>(reinterpret_cast<char*>(peers.base[rank]) + kArFlagBytes + result_off);
+    for (int64_t i = lo + (int64_t)blockIdx.x * kArThreads + threadIdx.x; i < hi; i += stride) {
+      float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      uint4 v[kArMaxWorld];
+#pragma unroll
+      for (int r = 0; r < kArMaxWorld; ++r)
+        if (r < world) v[r] = ld_volatile_v4(reinterpret_cast<const char*>(peers.base[r]) + kArFlagBytes + i * 16);
+#pragma unroll
+      for (int r = 0; r < kArMaxWorld; ++r) {
+        if (r < world) {
+          const uint32_t w[4] = {v[r].x, v[r].y, v[r].z, v[r].w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const float2 f = unpack2<BF16>(w[e]);
+            acc[2 * e] += f.x;
+            acc[2 * e + 1] += f.y;
+          }
+        }
+      }
+      uint4 o;
+      o.x = pack2<BF16>(acc[0], acc[1]); o.y = pack2<BF16>(acc[2], acc[3]);
+      o.z = pack2<BF16>(acc[4], acc[5]); o.w = pack2<BF16>(acc[6], acc[7]);
+      res[i] = o;
+    }
+  }
+  ar_barrier<true>(peers, rank, world, 1, epoch);  // slices published
+  for (int r = 0; r < world; ++r) {
+    const int64_t lo = r * slice, hi = min(n_vec, lo + slice);
+    const char* src = reinterpret_cast<const char*>(peers.base[r]) + kArFlagBytes + result_off;
+    for (int64_t i = lo + (int64_t)blockIdx.x * kArThreads + threadIdx.x; i < hi; i += stride)
+      reinterpret_cast<uint4*>(out)[i] = ld_volatile_v4(src + i * 16);
+  }
+  ar_barrier(peers, rank, world, 2, epoch);  // every peer has read my slice: payload and result may be rewritten
   if (threadIdx.x == 0) *my_epoch = epoch;
 }
 
@@ -153,6 +218,32 @@ extern "C" int cvllm_allreduce_oneshot(void* const* peer_bases_host, int rank, i
     allreduce_oneshot_kernel<true><<<blocks, kArThreads, 0, st>>>(peers, out, n_vec, rank, world);
   else
     allreduce_oneshot_kernel<false><<<blocks, kArThreads, 0, st>>>(peers, out, n_vec, rank, world);
+  CVLLM_CHECK_LAUNCH();
+  return CVLLM_OK;
+}
+
+// Two-shot form of the same sum for messages of a few MB: result_offset_bytes = distance from the payload start to a
+// result area of at least numel * 2 bytes inside every rank's buffer (same offset everywhere; the buffers must have
+// been allocated with room for it).  Same bits as cvllm_allreduce_oneshot.
+extern "C" int cvllm_allreduce_twoshot(void* const* peer_bases_host, int rank, int world, void* out, int64_t numel,
+                                       int dtype, int64_t result_offset_bytes, cvllm_stream_t stream) {
+  CVLLM_CHECK_ARG(peer_bases_host && out && world >= 1 && world <= kArMaxWorld && rank >= 0 && rank < world);
+  CVLLM_CHECK_ARG(numel >= 0 && numel % 8 == 0);
+  CVLLM_CHECK_ARG(result_offset_bytes >= numel * 2 && result_offset_bytes % 16 == 0);
+  CVLLM_CHECK_ARG(dtype == CVLLM_F16 || dtype == CVLLM_BF16);
+  CVLLM_CHECK_ALIGN(aligned16(out));
+  if (numel == 0) return CVLLM_OK;
+  ArPeers peers;
+  for (int r = 0; r < kArMaxWorld; ++r) peers.base[r] = r < world ? peer_bases_host[r] : nullptr;
+  const int64_t n_vec = numel / 8;
+  const int64_t slice = (n_vec + world - 1) / world;
+  int blocks = (int)((slice + kArThreads - 1) / kArThreads);
+  blocks = blocks < 1 ? 1 : (blocks > kArBlocks ? kArBlocks : blocks);
+  auto st = static_cast<cudaStream_t>(stream);
+  if (dtype == CVLLM_BF16)
+    allreduce_twoshot_kernel<true><<<blocks, kArThreads, 0, st>>>(peers, out, n_vec, result_offset_bytes, rank, world);
+  else
+    allreduce_twoshot_kernel<false><<<blocks, kArThreads, 0, st>>>(peers, out, n_vec, result_offset_bytes, rank, world);
   CVLLM_CHECK_LAUNCH();
   return CVLLM_OK;
 }

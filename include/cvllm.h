@@ -147,6 +147,12 @@ int cvllm_ipc_free(void* own_ptr);
  * has finished on this rank's stream. */
 int cvllm_allreduce_oneshot(void* const* peer_bases_host, int rank, int world, void* out,
                             int64_t numel, int dtype, cvllm_stream_t stream);
+/* The same sum in two steps for messages of a few MB at 4-8 ranks: rank r reduces slice r into a RESULT area of its
+ * own buffer (result_offset_bytes past the payload start, >= numel * 2, the same on every rank; allocate
+ * cvllm_ipc_alloc(payload + result)), publishes it, and every rank gathers the slices.  NVLink traffic per rank
+ * 2 x (world-1)/world x message instead of (world-1) x message; identical bits to the one-shot form. */
+int cvllm_allreduce_twoshot(void* const* peer_bases_host, int rank, int world, void* out,
+                            int64_t numel, int dtype, int64_t result_offset_bytes, cvllm_stream_t stream);
 
 /* ------------------------------------------------------------------------
  * Selection + compaction

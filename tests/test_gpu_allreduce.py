@@ -58,6 +58,14 @@ def test_oneshot_allreduce_world1(single_rank_group, dtype):
             graph.replay()
         torch.cuda.synchronize()
         assert torch.equal(out, st)
+        # the two-shot form (slice reduce + gather through the result area) gives the same bits
+        par2 = PeerAllReduce(max_bytes=1 << 20, device=dev, twoshot_min_bytes=0)
+        try:
+            for shape in ((64, 8192), (3, 40), (1, 8)):
+                x = torch.randn(shape, generator=g, device=dev).to(dtype)
+                assert torch.equal(par2.all_reduce(x.clone()), x)
+        finally:
+            par2.close()
         # too large for the staging buffer -> the process-group route, same result
         big = torch.randn((128, 8192), generator=g, device=dev).to(dtype)
         assert not par.fits(big)

@@ -42,11 +42,12 @@ def main():
     dist.init_process_group("nccl", device_id=dev)
     from compactor_vllm.layers.linear import PeerAllReduce, RowParallelLinear, shard_rows
 
-    par = PeerAllReduce(max_bytes=4 << 20)
+    par = PeerAllReduce(max_bytes=8 << 20, twoshot_min_bytes=1 << 62)  # one-shot only
+    par2 = PeerAllReduce(max_bytes=8 << 20, twoshot_min_bytes=0)      # two-shot only
     res = {"world": world, "checks": {}, "us": {}}
     g = torch.Generator(device=dev).manual_seed(100 + rank)
     ok = True
-    for rows in (1, 16, 64, 256):
+    for rows in (1, 16, 64, 256, 509):
         x = torch.randn((rows, 8192), generator=g, device=dev).bfloat16()
         got = par.all_reduce(x.clone())
         # fp32 reference: gather all partials, sum in rank order, round once
@@ -58,6 +59,10 @@ def main():
         for p in parts:
             acc += p.float()
         exact = torch.equal(got, acc.bfloat16())
+        got2 = par2.all_reduce(x.clone())
+        exact2 = torch.equal(got2, got)  # the two-shot form sums in the same order: same bits
+        res["checks"][f"twoshot_rows{rows}_equals_oneshot"] = exact2
+        ok &= exact2
         same = [torch.empty_like(got) for _ in range(world)]
         dist.all_gather(same, got)
         identical = all(torch.equal(same[0], s) for s in same)
@@ -72,6 +77,13 @@ def main():
         res["us"][f"peer_{rows}x8192"] = timed(lambda: par.all_reduce(xs))
         xn = x.clone()
         res["us"][f"nccl_{rows}x8192"] = timed(lambda: dist.all_reduce(xn))
+
+    # ragged slices (15 vectors over `world` ranks) and an empty slice (1 vector)
+    for shape in ((3, 40), (1, 8)):
+        xr = torch.randn(shape, generator=g, device=dev).bfloat16()
+        same_bits = torch.equal(par2.all_reduce(xr.clone()), par.all_reduce(xr.clone()))
+        res["checks"][f"twoshot_ragged_{shape[0]}x{shape[1]}"] = same_bits
+        ok &= same_bits
 
     # RowParallelLinear: sharded weight + peer all-reduce == unsharded GEMM (bf16 tolerance)
     gw = torch.Generator(device=dev).manual_seed(7)  # same seed on every rank: the full weight
@@ -124,10 +136,13 @@ def main():
         return timed(gr.replay) / reps
 
     with torch.no_grad():
-        for rows in (1, 16, 64, 128):
+        for rows in (1, 16, 64, 128, 256, 512):
             st = par.staging((rows, 8192), torch.bfloat16)
             st.normal_()
             res["us"][f"graph_peer_allreduce_{rows}x8192"] = graphed(lambda: par.reduce_staged(st))
+            st2 = par2.staging((rows, 8192), torch.bfloat16)
+            st2.normal_()
+            res["us"][f"graph_twoshot_allreduce_{rows}x8192"] = graphed(lambda: par2.reduce_staged(st2))
             xn = torch.randn((rows, 8192), device=dev).bfloat16()
             try:
                 res["us"][f"graph_nccl_allreduce_{rows}x8192"] = graphed(lambda: dist.all_reduce(xn))
@@ -146,6 +161,7 @@ def main():
     res["nccl_prefill_busbw_gbs"] = big.numel() * 2 * 2 * (world - 1) / world / (us * 1e-6) / 1e9
     res["ok"] = bool(ok)
     par.close()
+    par2.close()
     if rank == 0:
         print(json.dumps(res))
     dist.destroy_process_group()
