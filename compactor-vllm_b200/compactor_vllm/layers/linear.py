@@ -38,13 +38,16 @@ class PeerAllReduce:
         self.device = device or torch.device("cuda", torch.cuda.current_device())
         # One-shot reads (world-1) x message per rank, two-shot 2 x (world-1)/world x message plus one publishing
         # barrier (a system-scope fence): measured switch points on one 8 x B200 box (profiles/r01h_tp_allreduce_n8.json).
-        # 8 ranks: two-shot wins from ~3 MB (4 MB: 35.6 us vs 54.2 one-shot / 56.1 NCCL; 8 MB: 59 vs 73 NCCL) but
-        # its publishing fence costs ~17 us, so small messages stay one-shot (7.8 us at 16 KB vs 24.3);
-        # 2-4 ranks: the one-shot form is never slower up to 8 MB, where it meets NCCL.
+        # Measured per call inside a CUDA graph, [rows, 8192] bf16 (profiles/r01h_tp_allreduce*.json):
+        #   8 ranks: one-shot 7.8 / 10.6 / 19.2 us at 16 KB / 256 KB / 1 MB, two-shot 11.8 / 13.6 / 14.9 us -> switch
+        #            at 512 KB; 4 MB: 21.3 us (NCCL 56.0), 8 MB: 33.5 us (NCCL 73.1)
+        #   4 ranks: one-shot 12.3 / 17.6 us at 1 / 2 MB, two-shot 13.4 / 15.3 us -> switch at 1.5 MB; 8 MB 30.9 (NCCL 49.7)
+        #   2 ranks: both forms move the same bytes, the one-shot has one barrier less -> never two-shot
         if max_bytes is None:
             max_bytes = 8 << 20
         if twoshot_min_bytes is None:
-            twoshot_min_bytes = (3 << 20) if self.world >= 8 else (4 << 20) if self.world >= 6 else (1 << 62)
+            twoshot_min_bytes = ((512 << 10) if self.world >= 8 else (1536 << 10) if self.world >= 4
+                                 else (4 << 20) if self.world == 3 else (1 << 62))
         self.max_bytes = int(max_bytes)
         self.twoshot_min_bytes = int(twoshot_min_bytes)
         lib = N.lib()

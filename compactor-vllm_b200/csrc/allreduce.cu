@@ -46,18 +46,31 @@ __device__ __forceinline__ uint32_t ld_flag(const uint32_t* p) {
 // (phase, block, me); wait = spin on my own words until they reach it.  A peer can be at most one call ahead,
 // hence the >= comparison.
 // PUBLISH = true: data written by THIS kernel (by any thread of the block, before the leading __syncthreads) must be
-// visible to the peers that see the flag — a system-scope fence in front of the flag store (cumulative over the
-// block's writes through the barrier) and an acquire load on the polling side.
+// visible to the peers that see the flag.  The data lives in THIS rank's memory and peers read it with loads that
+// are served by this GPU's L2, so a gpu-scope fence (writes performed at the L2, cumulative over the block's writes
+// through the barrier) in front of the flag store is what is needed; a system-scope fence also waits for every
+// outstanding remote store (+1..3 us per call at 8 ranks, measured).  The 64-call back-to-back stress in
+// tools/tp_allreduce_check.py checks every output bit against the fp32 rank-order sum.  -DCVLLM_AR_SYSFENCE at
+// build time restores the formal .sys fence + acquire poll.
 template <bool PUBLISH = false>
 __device__ __forceinline__ void ar_barrier(const ArPeers& peers, int rank, int world, int phase, uint32_t epoch) {
   __syncthreads();
   if (threadIdx.x < world) {
     const int peer = threadIdx.x;
     const int word = kArBlocks + (phase * kArBlocks + blockIdx.x) * kArMaxWorld;
+#ifdef CVLLM_AR_SYSFENCE
     if (PUBLISH) __threadfence_system();
+#else
+    if (PUBLISH) __threadfence();
+#endif
     st_flag(reinterpret_cast<uint32_t*>(peers.base[peer]) + word + rank, epoch);
     const uint32_t* mine = reinterpret_cast<const uint32_t*>(peers.base[rank]) + word + peer;
-    if (PUBLISH) {
+#ifdef CVLLM_AR_SYSFENCE
+    constexpr bool kAcquirePoll = PUBLISH;
+#else
+    constexpr bool kAcquirePoll = false;
+#endif
+    if (kAcquirePoll) {
       uint32_t v;
       do {
         asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(mine) : "memory");
@@ -151,11 +164,21 @@ __global__ void __launch_bounds__(kArThreads) allreduce_twoshot_kernel(ArPeers p
     }
   }
   ar_barrier<true>(peers, rank, world, 1, epoch);  // slices published
-  for (int r = 0; r < world; ++r) {
-    const int64_t lo = r * slice, hi = min(n_vec, lo + slice);
-    const char* src = reinterpret_cast<const char*>(peers.base[r]) + kArFlagBytes + result_off;
-    for (int64_t i = lo + (int64_t)blockIdx.x * kArThreads + threadIdx.x; i < hi; i += stride)
-      reinterpret_cast<uint4*>(out)[i] = ld_volatile_v4(src + i * 16);
+  // gather: the loads from all owners are issued before the first store — one NVLink round trip per trip of the
+  // loop, not `world` dependent ones (the serial form cost ~12 us at 8 ranks whatever the message size)
+  for (int64_t j = (int64_t)blockIdx.x * kArThreads + threadIdx.x; j < slice; j += stride) {
+    uint4 v[kArMaxWorld];
+#pragma unroll
+    for (int r = 0; r < kArMaxWorld; ++r) {
+      const int64_t i = r * slice + j;
+      if (r < world && i < n_vec)
+        v[r] = ld_volatile_v4(reinterpret_cast<const char*>(peers.base[r]) + kArFlagBytes + result_off + i * 16);
+    }
+#pragma unroll
+    for (int r = 0; r < kArMaxWorld; ++r) {
+      const int64_t i = r * slice + j;
+      if (r < world && i < n_vec) reinterpret_cast<uint4*>(out)[i] = v[r];
+    }
   }
   ar_barrier(peers, rank, world, 2, epoch);  // every peer has read my slice: payload and result may be rewritten
   if (threadIdx.x == 0) *my_epoch = epoch;

@@ -85,6 +85,21 @@ def main():
         res["checks"][f"twoshot_ragged_{shape[0]}x{shape[1]}"] = same_bits
         ok &= same_bits
 
+    # stress: 64 back-to-back two-shot calls on fresh data (no host sync in between), every output checked against
+    # the fp32 rank-order sum — a stale slice (a fence that is too weak) shows up as a bit difference
+    xs_all = [torch.randn((96 + 8 * (i % 5), 8192), generator=g, device=dev).bfloat16() for i in range(64)]
+    outs = [par2.all_reduce(xi) for xi in xs_all]
+    stress_ok = True
+    for xi, oi in zip(xs_all, outs):
+        parts = [torch.empty_like(xi) for _ in range(world)]
+        dist.all_gather(parts, xi)
+        acc = torch.zeros(xi.shape, dtype=torch.float32, device=dev)
+        for pp in parts:
+            acc += pp.float()
+        stress_ok &= torch.equal(oi, acc.bfloat16())
+    res["checks"]["twoshot_stress_64_calls_bit_exact"] = bool(stress_ok)
+    ok &= bool(stress_ok)
+
     # RowParallelLinear: sharded weight + peer all-reduce == unsharded GEMM (bf16 tolerance)
     gw = torch.Generator(device=dev).manual_seed(7)  # same seed on every rank: the full weight
     W = (0.02 * torch.randn((8192, 8192), generator=gw, device=dev)).bfloat16()
