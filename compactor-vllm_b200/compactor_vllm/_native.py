@@ -22,6 +22,8 @@ _SIGNATURES = {
     "cvllm_abi_version": (C.c_int, []),
     "cvllm_last_error": (C.c_char_p, []),
     "cvllm_launch_count": (C.c_uint64, []),
+    "cvllm_set_test_option": (_i, [C.c_char_p, C.c_double]),
+    "cvllm_selftest_eig": (_i, [_p, _p, _p, _p, _i, _i, _p, _p]),
     "cvllm_decode_store_kv": (_i, [_p, _p, _i64, _i64, _i64, _i64, _p, _p, _p, _p, _p,
                                    _i, _i, _i, _i, _i, _i, _i, _p]),
     "cvllm_prefill_store_all": (_i, [_p, _p, _i64, _i64, _i64, _i64, _p, _p, _p, _p, _p, _p,
@@ -98,6 +100,11 @@ def lib() -> C.CDLL:
             raise NativeLibraryError("libcompactor_sm100.so ABI version mismatch")
         _lib = handle
     return _lib
+
+
+def set_test_option(name: str, value: float) -> None:
+    """Test / profiling switch of the library (include/cvllm.h: cvllm_set_test_option)."""
+    check(lib().cvllm_set_test_option(name.encode(), float(value)), f"cvllm_set_test_option({name})")
 
 
 def exported_symbols() -> list[str]:

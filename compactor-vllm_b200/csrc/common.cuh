@@ -8,6 +8,8 @@
 #include <stdint.h>
 #include <stdio.h>
 
+#include <atomic>
+
 #include "../../include/cvllm.h"
 
 namespace cvllm {
@@ -59,6 +61,31 @@ void note_launches(int n);
     CVLLM_CHECK_CUDA(cudaPeekAtLastError());                                   \
   } while (0)
 #define CVLLM_CHECK_LAUNCH() CVLLM_CHECK_LAUNCHES(1)
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a per-DEVICE property of a kernel: raise it once per
+// (kernel, device), so one process can drive several GPUs.  `mask` (one static per call site) has a
+// bit per device ordinal.  Not a stream operation: safe under CUDA-graph capture.
+inline cudaError_t ensure_max_dyn_smem(const void* func, int bytes, std::atomic<uint64_t>& mask) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  const uint64_t bit = 1ull << (dev & 63);
+  if (mask.load(std::memory_order_acquire) & bit) return cudaSuccess;
+  e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e == cudaSuccess) mask.fetch_or(bit, std::memory_order_release);
+  return e;
+}
+
+// Test / profiling switches, set only through cvllm_set_test_option (include/cvllm.h); the product path
+// never reads the environment.
+struct TestOptions {
+  std::atomic<int> prefill_v1{0};             // 1: force the one-head-per-CTA prefill kernel
+  std::atomic<float> prefill_threshold{-1.f}; // >= 0: lazy-rescale threshold of the prefill softmax
+  std::atomic<int> decode_mode{0};            // decode_attn.cu profiling modes (0 = product)
+  std::atomic<int> decode_slots{0};           // >= 2: cap the decode TMA ring depth
+  std::atomic<int> eig_trace{0};
+};
+TestOptions& test_options();
 
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 

@@ -597,10 +597,7 @@ static int launch_decode_attn(const void* q, void* out, const void* k_cache, con
 #ifdef CVLLM_DECODE_TRACE
   p.trace = g_decode_trace;
 #endif
-  {
-    static const int mode = [] { const char* e = getenv("CVLLM_DECODE_MODE"); return e ? atoi(e) : 0; }();
-    p.mode = mode;
-  }
+  p.mode = test_options().decode_mode.load(std::memory_order_relaxed);
 
   // 2-D maps over the flat [rows, D] caches; the row bound is not known to this ABI (only
   // mapped pages are ever addressed), so it is the largest int32 coordinate
@@ -623,20 +620,15 @@ static int launch_decode_attn(const void* q, void* out, const void* k_cache, con
   int slots = (int)(((size_t)kMaxSmem - fixed) / kSlotBytes);
   if (slots > kMaxSlots) slots = kMaxSlots;
   {
-    static const int env_slots = [] { const char* e = getenv("CVLLM_DECODE_SLOTS"); return e ? atoi(e) : 0; }();
-    if (env_slots >= 2 && env_slots < slots) slots = env_slots;  // profiling knob
+    const int cap = test_options().decode_slots.load(std::memory_order_relaxed);  // profiling knob
+    if (cap >= 2 && cap < slots) slots = cap;
   }
   p.slots = slots;
   const size_t smem = fixed + (size_t)slots * kSlotBytes;
-  // raise the dynamic-smem cap once per process (not a stream op; kept out of graph capture)
-  static bool attr_set = false;
-  if (!attr_set) {
-    CVLLM_CHECK_CUDA(cudaFuncSetAttribute(decode_attn_kernel<true, 128>,
-                                          cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxSmem));
-    CVLLM_CHECK_CUDA(cudaFuncSetAttribute(decode_attn_kernel<false, 128>,
-                                          cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxSmem));
-    attr_set = true;
-  }
+  // raise the dynamic-smem cap once per (kernel, device)
+  static std::atomic<uint64_t> attr_bf{0}, attr_h{0};
+  if (bf16) CVLLM_CHECK_CUDA(ensure_max_dyn_smem((const void*)decode_attn_kernel<true, 128>, kMaxSmem, attr_bf));
+  else CVLLM_CHECK_CUDA(ensure_max_dyn_smem((const void*)decode_attn_kernel<false, 128>, kMaxSmem, attr_h));
   if (bf16) {
     decode_attn_kernel<true, 128><<<C, kDecThreads, smem, st>>>(tm_k, tm_v, p);
   } else {

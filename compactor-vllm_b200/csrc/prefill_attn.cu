@@ -490,24 +490,26 @@ extern "C" int cvllm_prefill_attention(const void* q, const void* k, const void*
   p.scale_log2 = sm_scale * 1.4426950408889634f;
   p.rescale_threshold = kRescaleThreshold;
   // test hook: 0 forces an O rescale whenever a row max grows (exercises the correction path)
-  if (const char* e = getenv("CVLLM_PREFILL_THRESHOLD")) p.rescale_threshold = (float)atof(e);
+  {
+    const float t = test_options().prefill_threshold.load(std::memory_order_relaxed);
+    if (t >= 0.f) p.rescale_threshold = t;
+  }
 
   auto st = static_cast<cudaStream_t>(stream);
   // even GQA group: two query heads of one KV head per CTA, ping-ponged S accumulators
-  // (prefill_attn2.cu).  CVLLM_PREFILL_V1=1 forces the one-head-per-CTA kernel (tests cover both).
-  if ((HQ / HKV) % 2 == 0 && !getenv("CVLLM_PREFILL_V1"))
+  // (prefill_attn2.cu).  Test option "prefill_v1" forces the one-head-per-CTA kernel (tests cover both).
+  if ((HQ / HKV) % 2 == 0 && !test_options().prefill_v1.load(std::memory_order_relaxed))
     return cvllm_launch_prefill2(tm_q, tm_k, tm_v, tm_kc, tm_vc, out, seq_lens_bh, page_table,
                                  batch_mapping, cu_seqlens_q, B, HQ, HKV, PS, NLP, o_stride_n,
                                  max_seqlen_q, p.scale_log2, p.rescale_threshold, bf16, st);
   const size_t smem = sizeof(PrefillSmem) + 1024;
   const dim3 grid((max_seqlen_q + kBM - 1) / kBM, HQ, B);
+  static std::atomic<uint64_t> attr_bf{0}, attr_h{0};
   if (bf16) {
-    CVLLM_CHECK_CUDA(cudaFuncSetAttribute(prefill_attn_kernel<true>,
-                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CVLLM_CHECK_CUDA(ensure_max_dyn_smem((const void*)prefill_attn_kernel<true>, (int)smem, attr_bf));
     prefill_attn_kernel<true><<<grid, kPrefillThreads, smem, st>>>(tm_q, tm_k, tm_v, tm_kc, tm_vc, p);
   } else {
-    CVLLM_CHECK_CUDA(cudaFuncSetAttribute(prefill_attn_kernel<false>,
-                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CVLLM_CHECK_CUDA(ensure_max_dyn_smem((const void*)prefill_attn_kernel<false>, (int)smem, attr_h));
     prefill_attn_kernel<false><<<grid, kPrefillThreads, smem, st>>>(tm_q, tm_k, tm_v, tm_kc, tm_vc, p);
   }
   CVLLM_CHECK_LAUNCH();

@@ -388,30 +388,11 @@ int cvllm_launch_prefill2(const CUtensorMap& tm_q, const CUtensorMap& tm_k, cons
   p.rescale_threshold = rescale_threshold;
   const size_t smem = sizeof(Prefill2Smem) + 1024;
   const dim3 grid((max_seqlen_q + p2::kBM - 1) / p2::kBM, HQ / 2, B);
-  static bool attr_set = false;
-  if (!attr_set) {
-    CVLLM_CHECK_CUDA(cudaFuncSetAttribute(prefill_attn2_kernel<true>,
-                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    CVLLM_CHECK_CUDA(cudaFuncSetAttribute(prefill_attn2_kernel<false>,
-                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr_set = true;
-  }
+  static std::atomic<uint64_t> attr_bf{0}, attr_h{0};
+  if (bf16) CVLLM_CHECK_CUDA(ensure_max_dyn_smem((const void*)prefill_attn2_kernel<true>, (int)smem, attr_bf));
+  else CVLLM_CHECK_CUDA(ensure_max_dyn_smem((const void*)prefill_attn2_kernel<false>, (int)smem, attr_h));
   if (bf16) prefill_attn2_kernel<true><<<grid, p2::kThreads, smem, st>>>(tm_q, tm_k, tm_v, tm_kc, tm_vc, p);
   else prefill_attn2_kernel<false><<<grid, p2::kThreads, smem, st>>>(tm_q, tm_k, tm_v, tm_kc, tm_vc, p);
   CVLLM_CHECK_LAUNCH();
   return CVLLM_OK;
-}
-
-// debug aid (not part of include/cvllm.h): launch-relevant attributes of the paired kernel
-extern "C" int cvllm_debug_prefill2_attrs(int* out) {
-  cudaFuncAttributes a;
-  if (cudaFuncGetAttributes(&a, prefill_attn2_kernel<true>) != cudaSuccess) return -1;
-  out[0] = a.numRegs; out[1] = a.maxThreadsPerBlock; out[2] = (int)a.sharedSizeBytes;
-  out[3] = a.maxDynamicSharedSizeBytes; out[4] = (int)a.localSizeBytes; out[5] = (int)a.constSizeBytes;
-  out[6] = (int)(sizeof(Prefill2Smem) + 1024);
-  int dev = 0, v = 0;
-  cudaGetDevice(&dev);
-  cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
-  out[7] = v;
-  return 0;
 }

@@ -325,12 +325,9 @@ static int launch_rope(const RopeParams& p, bool norm, bool sketch, int n_tiles,
   const size_t smem = sketch ? sizeof(RopeSmem) : 0;
 #define CVLLM_ROPE_LAUNCH(NORM, SK)                                                                \
   do {                                                                                             \
-    static bool attr = false;                                                                      \
-    if (SK && !attr) {                                                                             \
-      CVLLM_CHECK_CUDA(cudaFuncSetAttribute(rope_qk_kernel<BF16, NORM, SK>,                        \
-                                            cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-      attr = true;                                                                                 \
-    }                                                                                              \
+    static std::atomic<uint64_t> attr{0};                                                          \
+    if (SK)                                                                                        \
+      CVLLM_CHECK_CUDA(ensure_max_dyn_smem((const void*)rope_qk_kernel<BF16, NORM, SK>, (int)smem, attr)); \
     int per_sm = 1;                                                                                \
     CVLLM_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(                                \
         &per_sm, rope_qk_kernel<BF16, NORM, SK>, kRopeThreads, smem));                             \

@@ -20,6 +20,11 @@ static std::atomic<uint64_t> g_launches{0};
 void note_launches(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
 uint64_t launches() { return g_launches.load(std::memory_order_relaxed); }
 
+TestOptions& test_options() {
+  static TestOptions opts;
+  return opts;
+}
+
 int sm_count() {
   static int cached[64] = {0};
   int dev = 0;
@@ -88,3 +93,17 @@ int make_tmap_16b(CUtensorMap* map, const void* base, int rank, const uint64_t* 
 extern "C" int cvllm_abi_version(void) { return CVLLM_ABI_VERSION; }
 extern "C" const char* cvllm_last_error(void) { return cvllm::g_last_error; }
 extern "C" uint64_t cvllm_launch_count(void) { return cvllm::launches(); }
+
+extern "C" int cvllm_set_test_option(const char* name, double value) {
+  if (!name) return CVLLM_E_ARG;
+  auto& o = cvllm::test_options();
+  if (!strcmp(name, "prefill_v1")) o.prefill_v1 = (int)value;
+  else if (!strcmp(name, "prefill_threshold")) o.prefill_threshold = (float)value;
+  else if (!strcmp(name, "decode_mode")) o.decode_mode = (int)value;
+  else if (!strcmp(name, "decode_slots")) o.decode_slots = (int)value;
+  else {
+    cvllm::set_last_error("unknown test option");
+    return CVLLM_E_ARG;
+  }
+  return CVLLM_OK;
+}

@@ -551,14 +551,9 @@ extern "C" int cvllm_chunk_attn_scores(const void* q, const void* k, int64_t q_s
   const int64_t items = (int64_t)B * HKV * grid_chunks;
   CVLLM_CHECK_SUPPORTED(items < (1ll << 31));
   const int grid = (int)(items < sm_count() ? items : sm_count());
-  static bool attr_set = false;  // 2 K buffers = 80 KB dynamic smem (not a stream op: safe under capture)
-  if (!attr_set) {
-    CVLLM_CHECK_CUDA(cudaFuncSetAttribute(chunk_scores_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          2 * kScSmem));
-    CVLLM_CHECK_CUDA(cudaFuncSetAttribute(chunk_scores_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          2 * kScSmem));
-    attr_set = true;
-  }
+  static std::atomic<uint64_t> attr_bf{0}, attr_h{0};  // 2 K buffers = 80 KB dynamic smem
+  if (dtype == CVLLM_BF16) CVLLM_CHECK_CUDA(ensure_max_dyn_smem((const void*)chunk_scores_kernel<true>, 2 * kScSmem, attr_bf));
+  else CVLLM_CHECK_CUDA(ensure_max_dyn_smem((const void*)chunk_scores_kernel<false>, 2 * kScSmem, attr_h));
   if (dtype == CVLLM_BF16) chunk_scores_kernel<true><<<grid, kScThreads, 2 * kScSmem, st>>>(p);
   else chunk_scores_kernel<false><<<grid, kScThreads, 2 * kScSmem, st>>>(p);
   CVLLM_CHECK_LAUNCH();

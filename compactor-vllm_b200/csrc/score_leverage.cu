@@ -199,7 +199,11 @@ __global__ void __launch_bounds__(kLevThreads, 2) leverage_gram_kernel(const Lev
     // 3 m-tiles (16 sketch rows) x 6 n-tiles (8 sketch cols) = 18 output tiles over 8 warps
     for (int tile = warp; tile < 18; tile += kLevThreads / 32) {
       const int mt = tile / 6, nn = tile - mt * 6;
-      float acc[4] = {0.f, 0.f, 0.f, 0.f};
+      // the accumulator is CARRIED across token tiles (not summed per tile and added): one sequential
+      // k16 chain over the whole chunk, the order a non-split-K library GEMM accumulates in — the Gram is
+      // rounded to 16 bit next, and on low-rank keys one flipped ulp there moves a chunk's scores by O(1)
+      const int gi = mt * 16 + r, gj = nn * 8 + 2 * j;
+      float acc[4] = {sm.g[gi][gj], sm.g[gi][gj + 1], sm.g[gi + 8][gj], sm.g[gi + 8][gj + 1]};
       const uint16_t* a_lo = sm.xt[mt * 16 + r];
       const uint16_t* a_hi = sm.xt[mt * 16 + r + 8];
       const uint16_t* b_r = sm.xt[nn * 8 + r];
@@ -212,11 +216,10 @@ __global__ void __launch_bounds__(kLevThreads, 2) leverage_gram_kernel(const Lev
         const uint32_t b1 = *reinterpret_cast<const uint32_t*>(b_r + k0 + 8 + 2 * j);
         mma16816<BF16>(acc, a0, a1, a2, a3, b0, b1);
       }
-      const int gi = mt * 16 + r, gj = nn * 8 + 2 * j;
-      sm.g[gi][gj] += acc[0];
-      sm.g[gi][gj + 1] += acc[1];
-      sm.g[gi + 8][gj] += acc[2];
-      sm.g[gi + 8][gj + 1] += acc[3];
+      sm.g[gi][gj] = acc[0];
+      sm.g[gi][gj + 1] = acc[1];
+      sm.g[gi + 8][gj] = acc[2];
+      sm.g[gi + 8][gj + 1] = acc[3];
     }
     __syncthreads();
   }
@@ -230,205 +233,355 @@ __global__ void __launch_bounds__(kLevThreads, 2) leverage_gram_kernel(const Lev
   if (tid < kSk) p.mean[(int64_t)(ch * p.HKV + h) * kSk + tid] = sm.mean[tid];
 }
 
-// ---- kernel 2: symmetric eigendecomposition, one WARP per matrix — Householder tridiagonalisation, accumulation of the
-// reflectors and implicit-shift QL (the EISPACK tred2 / tql2 pair, restated for a warp: lanes own
-// matrix rows, the scalar recurrences are computed redundantly by every lane).  ~1900 dependent
-// rotations of ~50 cycles each; a block-wide parallel cyclic Jacobi (the first version of this kernel)
-// moved 27 MB through shared memory per matrix, this moves 2.7 MB.
-// out: sv[(ch*HKV+h)][48][48] = round16(V |lam|^-1/2)   (compactor.py:197: S of a symmetric G is |lam|);
+// ---- kernel 2: symmetric eigendecomposition in fp64, one 128-thread CTA per 48x48 matrix ----
+// Why fp64: the reference's gesvda result agrees with the EXACT (fp64) eigendecomposition of the same
+// fp32 Gram to 99.3 % of the scores within 2e-2 on low-rank keys, while any norm-wise backward-stable
+// fp32 solver (cuSOLVER gesvd / gesvdj, and round 1's fp32 QL here) only reaches 60-85 %
+// (profiles/r02a_leverage_selfdistance_before.json): |lam| ranges over 1e-2 .. 1e5, and an absolute
+// error of eps32 * |lam|_max ~ 1e-2 destroys the small eigenpairs that dominate x^T |G|^-1 x.
+//
+// Structure (EISPACK tred2 / tql2 restated for a CTA):
+//   phase 1  all 4 warps: Householder reduction to tridiagonal form (matvec and rank-2 update spread over
+//            128 threads, lanes own COLUMNS so every shared-memory access is conflict-free).
+//   phase 2  warps 1-3: accumulate the reflectors into Z (in place)        } concurrently
+//   phase 3  warp 0: implicit-shift QL on (d, e) ONLY — the rotations do   }
+//            not depend on Z, so they are streamed through a ring in shared memory as (c, s) pairs, one
+//            sweep at a time, and warps 1-2 apply them to the rows of Z behind the producer.
+// The QL recurrence is the latency chain (~2000 dependent rotations).  It is rewritten so that one
+// rotation costs fma -> rsqrt -> mul on the dependent path:  with r^2 = p^2 + e_i^2, c = p/r, s = e_i/r,
+//   p_next = c d_i - s (c_prev e_i) = (p d_i - e_i^2 c_prev) / r,
+// and the numerator does not wait for 1/r.  1/r = rsqrt.approx.f64 + one third-order (Halley) step.
+// out: sv[mat][48][48] = round16(V |lam|^-1/2)   (compactor.py:197: S of a symmetric G is |lam|);
 // the column (eigenpair) order is arbitrary, the score sums over all of them.
-constexpr int kQlWarps = 16;  // matrices per CTA: few, fat CTAs block few SMs while attention runs beside them
-struct QlSmem {
-  float a[kSk][kSk + 1];
-  float d[kSk], e[kSk], hh[kSk], u[kSk], q[kSk];
+constexpr int kEigThreads = 128;
+constexpr int kEigRing = 1024;  // (c, s) entries; one sweep needs <= 48
+struct EigSmem {
+  double a[kSk][kSk + 1];  // A, then Z in place
+  double d[kSk], e[kSk], hh[kSk], hinv[kSk], u[kSk], q[kSk];
+  double part[2][64];
+  double2 ring[kEigRing];
+  double2 pr[kSk];  // (p_i, 1/r_i) of the current QL sweep
+  int produced, done;
+  int consumed[2];
 };
 
-__device__ __forceinline__ float rsqrt_nr(float x) {  // MUFU.RSQ + one Newton step; 0 -> 0
-  if (!(x > 0.f)) return 0.f;
-  const float y = rsqrtf(x);
-  return y * fmaf(-0.5f * x * y, y, 1.5f);
+__device__ __forceinline__ double warp_sum_d(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
 }
+__device__ __forceinline__ double rsqrt64(double x) {  // x > 0, normal: seed 2^-22, Halley -> fp64
+  double y;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+  const double e = fma(-x * y, y, 1.0);
+  return fma(y * e, fma(0.375, e, 0.5), y);
+}
+__device__ __forceinline__ double rcp64(double x) {  // x != 0, normal
+  double y;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+  double e = fma(-x, y, 1.0);
+  y = fma(y, e, y);
+  e = fma(-x, y, 1.0);
+  return fma(y, e, y);
+}
+__device__ __forceinline__ void bar_sync(int id, int count) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory");
+}
+__device__ __forceinline__ int ld_volatile_s(const int* p) { return *reinterpret_cast<const volatile int*>(p); }
+__device__ __forceinline__ void st_volatile_s(int* p, int v) { *reinterpret_cast<volatile int*>(p) = v; }
 
 template <bool BF16>
-__global__ void __launch_bounds__(kQlWarps * 32) leverage_eigql_kernel(const float* __restrict__ gram,
-                                                                      float* __restrict__ sv_out,
-                                                                      const int32_t* __restrict__ chunk_offsets,
-                                                                      int HKV, int mats) {
-  extern __shared__ __align__(16) unsigned char ql_smem_raw[];
-  QlSmem* sm_all = reinterpret_cast<QlSmem*>(ql_smem_raw);
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int mat = blockIdx.x * kQlWarps + warp;
+__global__ void __launch_bounds__(kEigThreads) leverage_eig_kernel(const float* __restrict__ gram,
+                                                                   float* __restrict__ sv_out,
+                                                                   const int32_t* __restrict__ chunk_offsets,
+                                                                   int HKV, int mats, double* __restrict__ dbg_lam,
+                                                                   double* __restrict__ dbg_vec,
+                                                                   long long* __restrict__ dbg_clk) {
+  __shared__ __align__(16) EigSmem s;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int mat = blockIdx.x;
   if (mat >= mats) return;
-  const int ch = mat / HKV;
-  if (chunk_offsets[ch + 1] - chunk_offsets[ch] <= 0) return;
-  QlSmem& s = sm_all[warp];
+  if (chunk_offsets) {
+    const int ch = mat / HKV;
+    if (chunk_offsets[ch + 1] - chunk_offsets[ch] <= 0) return;
+  }
   constexpr int n = kSk;
+  constexpr int R1 = kEigRing - 1;
   const float* gin = gram + (int64_t)mat * n * n;
-  for (int i = lane; i < n * n; i += 32) s.a[i / n][i % n] = gin[i];
-  __syncwarp();
-  const int j0 = lane, j1 = lane + 32;  // the two rows (or columns) of this lane; j1 valid for lane < 16
-  const bool has1 = j1 < n;
+  for (int i = tid; i < n * n; i += kEigThreads) s.a[i / n][i % n] = (double)gin[i];
+  if (tid == 0) { s.produced = 0; s.done = 0; s.consumed[0] = 0; s.consumed[1] = 0; }
+  __syncthreads();
+  if (dbg_clk && tid == 0) dbg_clk[mat * 6 + 0] = clock64();
 
-  // ---- Householder reduction to tridiagonal form; u^(i) is parked in column i (rows < i) ----
-  for (int i = n - 1; i >= 2; --i) {
-    float x0 = (j0 < i) ? s.a[i][j0] : 0.f;
-    float x1 = (has1 && j1 < i) ? s.a[i][j1] : 0.f;
-    const float scale = warp_sum(fabsf(x0) + fabsf(x1));
-    if (scale == 0.f) {  // row already reduced: H_i = I
-      if (lane == 0) { s.e[i] = 0.f; s.hh[i] = 0.f; s.d[i] = s.a[i][i]; }
+  // ---- phase 1: Householder reduction to tridiagonal form; u^(i) is parked in column i (rows < i) ----
+  {
+    const int col = tid & 63, half = tid >> 6;
+    for (int i = n - 1; i >= 2; --i) {
+      // every warp forms the reflector of row i redundantly (no broadcast round trip)
+      double x0 = (lane < i) ? s.a[i][lane] : 0.0;
+      double x1 = (lane + 32 < i) ? s.a[i][lane + 32] : 0.0;
+      const double h = warp_sum_d(fma(x0, x0, x1 * x1));
+      if (!(h > 1e-280)) {  // row already reduced (or not finite): H_i = I.  Uniform over the CTA.
+        if (tid == 0) { s.e[i] = 0.0; s.hh[i] = 0.0; s.hinv[i] = 0.0; s.d[i] = s.a[i][i]; }
+        continue;
+      }
+      const double f = s.a[i][i - 1];
+      const double g = -copysign(h * rsqrt64(h), f);
+      const double hi = h - f * g;
+      const double rh = rcp64(hi);
+      if (lane == ((i - 1) & 31)) {
+        if (i - 1 < 32) x0 = f - g; else x1 = f - g;
+      }
+      if (warp == 0) {
+        if (lane < i) { s.u[lane] = x0; s.a[lane][i] = x0; }
+        if (lane + 32 < i) { s.u[lane + 32] = x1; s.a[lane + 32][i] = x1; }
+        if (lane == 0) { s.e[i] = g; s.hh[i] = hi; s.hinv[i] = rh; s.d[i] = s.a[i][i]; }
+      }
+      __syncthreads();
+      // p = A u / h: thread (col, half) sums rows k = half, half+2, ... of column col (A is symmetric)
+      if (col < i) {
+        double acc0 = 0.0, acc1 = 0.0;
+        int k = half;
+        for (; k + 2 < i; k += 4) {
+          acc0 = fma(s.a[k][col], s.u[k], acc0);
+          acc1 = fma(s.a[k + 2][col], s.u[k + 2], acc1);
+        }
+        for (; k < i; k += 2) acc0 = fma(s.a[k][col], s.u[k], acc0);
+        s.part[half][col] = acc0 + acc1;
+      }
+      __syncthreads();
+      const double p0 = (lane < i) ? (s.part[0][lane] + s.part[1][lane]) * rh : 0.0;
+      const double p1 = (lane + 32 < i) ? (s.part[0][lane + 32] + s.part[1][lane + 32]) * rh : 0.0;
+      const double K = warp_sum_d(fma(x0, p0, x1 * p1)) * 0.5 * rh;
+      if (warp == 0) {
+        if (lane < i) s.q[lane] = fma(-K, x0, p0);
+        if (lane + 32 < i) s.q[lane + 32] = fma(-K, x1, p1);
+      }
+      __syncthreads();
+      // A <- A - u q^T - q u^T on the leading i x i block (kept fully symmetric)
+      if (col < i) {
+        const double uc = s.u[col], qc = s.q[col];
+        for (int j = half; j < i; j += 2) s.a[j][col] -= fma(s.u[j], qc, s.q[j] * uc);
+      }
+      __syncthreads();
+    }
+    if (tid == 0) {
+      s.d[0] = s.a[0][0]; s.d[1] = s.a[1][1];
+      s.e[1] = s.a[1][0]; s.e[0] = 0.0;
+      s.a[0][0] = 1.0;
+    }
+    __syncthreads();
+  }
+
+  if (dbg_clk && tid == 0) dbg_clk[mat * 6 + 1] = clock64();
+  if (warp == 0) {
+    // ---- phase 3 (producer): implicit-shift QL on (d, e); rotations -> ring ----
+    {
+      const double e0 = s.e[lane + 1];
+      const double e1 = (lane + 33 < n) ? s.e[lane + 33] : 0.0;
       __syncwarp();
-      continue;
+      s.e[lane] = e0;
+      if (lane + 32 < n) s.e[lane + 32] = e1;
+      __syncwarp();
     }
-    const float inv = 1.f / scale;
-    x0 *= inv; x1 *= inv;
-    float h = warp_sum(x0 * x0 + x1 * x1);
-    const float f = (i - 1 < 32) ? __shfl_sync(0xffffffffu, x0, i - 1) : __shfl_sync(0xffffffffu, x1, i - 33);
-    const float g = -copysignf(sqrtf(h), f);
-    h -= f * g;
-    if (j0 == i - 1) x0 = f - g;
-    if (j1 == i - 1) x1 = f - g;
-    if (j0 < i) { s.u[j0] = x0; s.a[j0][i] = x0; }
-    if (has1 && j1 < i) { s.u[j1] = x1; s.a[j1][i] = x1; }
-    if (lane == 0) { s.e[i] = scale * g; s.hh[i] = h; s.d[i] = s.a[i][i]; }
-    __syncwarp();
-    // p = A u / h  (rows >= i compute garbage that is never used)
-    float p0 = 0.f, p1 = 0.f;
-    for (int k = 0; k < i; ++k) {
-      const float uk = s.u[k];
-      p0 = fmaf(s.a[j0][k], uk, p0);
-      if (has1) p1 = fmaf(s.a[j1][k], uk, p1);
-    }
-    const float rh = 1.f / h;
-    p0 *= rh; p1 *= rh;
-    const float K = warp_sum(((j0 < i) ? x0 * p0 : 0.f) + ((has1 && j1 < i) ? x1 * p1 : 0.f)) * 0.5f * rh;
-    const float q0 = p0 - K * x0, q1 = p1 - K * x1;
-    if (j0 < i) s.q[j0] = q0;
-    if (has1 && j1 < i) s.q[j1] = q1;
-    __syncwarp();
-    // A <- A - u q^T - q u^T on the leading i x i block (kept fully symmetric)
-    for (int k = 0; k < i; ++k) {
-      const float uk = s.u[k], qk = s.q[k];
-      if (j0 < i) s.a[j0][k] -= fmaf(x0, qk, q0 * uk);
-      if (has1 && j1 < i) s.a[j1][k] -= fmaf(x1, qk, q1 * uk);
-    }
-    __syncwarp();
-  }
-  if (lane == 0) {
-    s.d[0] = s.a[0][0]; s.d[1] = s.a[1][1];
-    s.e[1] = s.a[1][0]; s.e[0] = 0.f;
-    s.a[0][0] = 1.f;
-  }
-  __syncwarp();
-
-  // ---- Z = H_{n-1} ... H_2, built in place: lanes own columns ----
-  for (int i = 2; i <= n; ++i) {
-    // row / column i-1 of the growing block become the identity (column i-1 held u^(i-1), consumed)
-    if (j0 < i - 1) { s.a[i - 1][j0] = 0.f; s.a[j0][i - 1] = 0.f; }
-    if (has1 && j1 < i - 1) { s.a[i - 1][j1] = 0.f; s.a[j1][i - 1] = 0.f; }
-    if (lane == 0) s.a[i - 1][i - 1] = 1.f;
-    __syncwarp();
-    if (i < n) {
-      const float h = s.hh[i];
-      if (h != 0.f) {
-        float g0 = 0.f, g1 = 0.f;
-        for (int k = 0; k < i; ++k) {
-          const float uk = s.a[k][i];
-          g0 = fmaf(uk, s.a[k][j0], g0);
-          if (has1) g1 = fmaf(uk, s.a[k][j1], g1);
-        }
-        const float rh = 1.f / h;
-        g0 *= rh; g1 *= rh;
-        for (int k = 0; k < i; ++k) {
-          const float uk = s.a[k][i];
-          if (j0 < i) s.a[k][j0] = fmaf(-g0, uk, s.a[k][j0]);
-          if (has1 && j1 < i) s.a[k][j1] = fmaf(-g1, uk, s.a[k][j1]);
-        }
+    double fsh = 0.0, tst1 = 0.0;
+    int prod = 0;
+    const double eps = 2.3e-13;  // 2^-42: |lam| is needed to ~1e-4 relative at |lam| >= reg = 5e-3
+    for (int l = 0; l < n; ++l) {
+      tst1 = fmax(tst1, fabs(s.d[l]) + fabs(s.e[l]));
+      // first m >= l with a negligible e[m] (e[n-1] == 0 ends the scan): two ballots instead of a serial walk
+      int m;
+      {
+        const double thr = eps * tst1;
+        const bool n0 = (lane >= l) && !(fabs(s.e[lane]) > thr);
+        const bool n1 = (lane + 32 >= l) && (lane + 32 >= n || !(fabs(s.e[lane + 32 < n ? lane + 32 : n - 1]) > thr));
+        const unsigned b0 = __ballot_sync(0xffffffffu, n0), b1 = __ballot_sync(0xffffffffu, n1);
+        m = b0 ? (__ffs(b0) - 1) : (32 + __ffs(b1) - 1);
+        if (m > n - 1) m = n - 1;
+      }
+      if (m > l) {
+        int iter = 0;
+        double el_abs;
+        do {
+          ++iter;
+          const double g0 = s.d[l], el = s.e[l], el1 = s.e[l + 1];
+          const double pp = (s.d[l + 1] - g0) * rcp64(2.0 * el);
+          const double x2 = fma(pp, pp, 1.0);
+          double rr = x2 * rsqrt64(x2);
+          if (pp < 0.0) rr = -rr;
+          const double ppr = pp + rr;
+          const double inv = rcp64(ppr);
+          const double dl = el * inv, dl1 = el * ppr;
+          const double hs = g0 - dl;
+          const double dj0 = s.d[lane], dj1 = (lane + 32 < n) ? s.d[lane + 32] : 0.0;
+          __syncwarp();
+          if (lane >= l + 2) s.d[lane] = dj0 - hs;
+          if (lane + 32 >= l + 2 && lane + 32 < n) s.d[lane + 32] = dj1 - hs;
+          if (lane == 0) { s.d[l] = dl; s.d[l + 1] = dl1; }
+          __syncwarp();
+          fsh += hs;
+          double p = s.d[m];
+          // ring space for this sweep: header + (m - l) rotations
+          const int need = m - l + 1;
+          while (prod + need - min(ld_volatile_s(&s.consumed[0]), ld_volatile_s(&s.consumed[1])) > kEigRing)
+            __nanosleep(64);
+          if (lane == 0) s.ring[prod & R1] = make_double2((double)l, (double)m);
+          // Warps issue in order, so anything between two links of the dependent chain delays it.  The loop
+          // therefore carries ONLY the recurrence (12 fp64 ops, p -> r^2 -> 1/r -> p on the chain) and parks
+          // (p_i, 1/r_i) in shared memory; the new d / e entries and the (c, s) ring records of the whole sweep
+          // are then formed by the lanes in parallel, one rotation per lane.  198 -> 86 cycles per rotation
+          // (tools/ubench/ql_chain.cu).
+          {
+            double c = 1.0;
+            double ei = s.e[m - 1], di = s.d[m - 1];
+            for (int i = m - 1; i >= l; --i) {
+              const double ein = (i > l) ? s.e[i - 1] : 0.0, din = (i > l) ? s.d[i - 1] : 0.0;  // prefetch
+              const double t = ei * ei;
+              const double r2 = fma(p, p, fma(ei, ei, 1e-300));  // > 0: no guard on the chain
+              const double qv = fma(p, di, -(t * c));            // r (c_new d_i - s_new g): does not wait for 1/r
+              double y;
+              asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(r2));
+              const double er = fma(-r2 * y, y, 1.0);
+              const double ri = fma(y * er, fma(0.375, er, 0.5), y);
+              if (lane == 0) s.pr[i] = make_double2(p, ri);
+              c = p * ri;
+              p = ri * qv;
+              ei = ein; di = din;
+            }
+          }
+          __syncwarp();
+          // rotation i = m-1-k on lane k (and k+32): reads first, then writes (e[i+1] is another lane's e_i)
+          double o_e[2], o_d[2], o_c[2], o_s[2];
+#pragma unroll
+          for (int u = 0; u < 2; ++u) {
+            const int k = lane + 32 * u, i = m - 1 - k;
+            o_e[u] = o_d[u] = o_c[u] = o_s[u] = 0.0;
+            if (i >= l) {
+              const double2 a = s.pr[i];
+              const double e_i = s.e[i], d_i = s.d[i];
+              const double c_i = a.x * a.y, s_i = e_i * a.y;
+              double c_p = 1.0, s_p = 0.0;
+              if (i < m - 1) {
+                const double2 b = s.pr[i + 1];
+                c_p = b.x * b.y;
+                s_p = s.e[i + 1] * b.y;
+              }
+              const double g = c_p * e_i, h = c_p * a.x;
+              const double r = fma(a.x, a.x, e_i * e_i) * a.y;
+              o_e[u] = s_p * r;
+              o_d[u] = h + s_i * fma(c_i, g, s_i * d_i);
+              o_c[u] = c_i;
+              o_s[u] = s_i;
+            }
+          }
+          __syncwarp();
+#pragma unroll
+          for (int u = 0; u < 2; ++u) {
+            const int k = lane + 32 * u, i = m - 1 - k;
+            if (i >= l) {
+              s.e[i + 1] = o_e[u];
+              s.d[i + 1] = o_d[u];
+              s.ring[(prod + 1 + k) & R1] = make_double2(o_c[u], o_s[u]);
+            }
+          }
+          __syncwarp();
+          // s_l, s_{l+1}, c_l, c_{l+2} of this sweep (absent rotations: s = 0, c = 1)
+          const int nrot = m - l;
+          const double2 q0 = s.ring[(prod + nrot) & R1];
+          const double sn = q0.y, c = q0.x;
+          const double s2 = (nrot >= 2) ? s.ring[(prod + nrot - 1) & R1].y : 0.0;
+          const double c3 = (nrot >= 3) ? s.ring[(prod + nrot - 2) & R1].x : 1.0;
+          const double pe = -sn * s2 * c3 * el1 * inv;  // = -s s2 c3 e[l+1] e[l] / d[l+1] with d[l+1] = e[l] (pp + rr)
+          el_abs = fabs(sn * pe);
+          __syncwarp();
+          if (lane == 0) { s.e[l] = sn * pe; s.d[l] = c * pe; }
+          prod += need;
+          __threadfence_block();
+          if (lane == 0) st_volatile_s(&s.produced, prod);
+          __syncwarp();
+        } while (el_abs > eps * tst1 && iter < 60);
       }
       __syncwarp();
+      if (lane == 0) { s.d[l] += fsh; s.e[l] = 0.0; }
+      __syncwarp();
     }
-  }
-
-  // ---- implicit-shift QL on (d, e); rotations accumulated into Z (lanes own rows) ----
-  {
-    const float e0 = s.e[j0 + 1 < n ? j0 + 1 : 0];
-    const float e1 = (has1 && j1 + 1 < n) ? s.e[j1 + 1] : 0.f;
-    __syncwarp();
-    s.e[j0] = e0;  // j0 + 1 < n always holds for j0 <= 31
-    if (has1) s.e[j1] = e1;
-    __syncwarp();
-  }
-  float fsh = 0.f, tst1 = 0.f;
-  const float eps = 1.1920929e-7f;
-  for (int l = 0; l < n; ++l) {
-    tst1 = fmaxf(tst1, fabsf(s.d[l]) + fabsf(s.e[l]));
-    int m = l;
-    while (m < n && fabsf(s.e[m]) > eps * tst1) ++m;  // e[n-1] == 0 ends the scan
-    if (m > l) {
-      int iter = 0;
-      float el_abs;
-      do {
-        ++iter;
-        const float g0 = s.d[l], el = s.e[l], el1 = s.e[l + 1];
-        float pp = (s.d[l + 1] - g0) / (2.f * el);
-        float rr = sqrtf(fmaf(pp, pp, 1.f));
-        if (pp < 0.f) rr = -rr;
-        const float dl = el / (pp + rr), dl1 = el * (pp + rr);
-        const float hs = g0 - dl;
-        const float dj0 = s.d[j0], dj1 = has1 ? s.d[j1] : 0.f;
-        float pcur = s.d[m];
-        __syncwarp();
-        if (j0 >= l + 2) s.d[j0] = dj0 - hs;
-        if (has1 && j1 >= l + 2) s.d[j1] = dj1 - hs;
-        if (lane == 0) { s.d[l] = dl; s.d[l + 1] = dl1; }
-        __syncwarp();
-        if (m >= l + 2 && m < n) pcur = s.d[m];  // d[m] was shifted by hs above
-        else if (m == l + 1) pcur = dl1;
-        fsh += hs;
-        float c = 1.f, c2 = 1.f, c3 = 1.f, sn = 0.f, s2 = 0.f;
-        // column m of Z is carried in registers from one rotation to the next
-        float z0 = s.a[j0][m], z1 = has1 ? s.a[j1][m] : 0.f;
-        float ei = s.e[m - 1], di = s.d[m - 1];
-        for (int i = m - 1; i >= l; --i) {
-          const float ein = (i > l) ? s.e[i - 1] : 0.f, din = (i > l) ? s.d[i - 1] : 0.f;  // prefetch
-          c3 = c2; c2 = c; s2 = sn;
-          const float g = c * ei, h = c * pcur;
-          const float x2 = fmaf(pcur, pcur, ei * ei);
-          const float ri = rsqrt_nr(x2);
-          const float r = x2 * ri;
-          sn = ei * ri;
-          c = pcur * ri;
-          pcur = c * di - sn * g;
-          if (lane == 0) { s.e[i + 1] = s2 * r; s.d[i + 1] = h + sn * (c * g + sn * di); }
-          // Z[:, i+1] = sn Z[:, i] + c Z[:, i+1];  Z[:, i] = c Z[:, i] - sn Z[:, i+1]
-          const float y0 = s.a[j0][i];
-          s.a[j0][i + 1] = fmaf(sn, y0, c * z0);
-          z0 = fmaf(c, y0, -sn * z0);
-          if (has1) {
-            const float y1 = s.a[j1][i];
-            s.a[j1][i + 1] = fmaf(sn, y1, c * z1);
-            z1 = fmaf(c, y1, -sn * z1);
+    __threadfence_block();
+    if (lane == 0) st_volatile_s(&s.done, 1);
+    if (dbg_clk && lane == 0) { dbg_clk[mat * 6 + 2] = clock64(); dbg_clk[mat * 6 + 5] = prod; }
+  } else {
+    // ---- phase 2 (warps 1-3): Z = H_{n-1} ... H_2, built in place; thread owns (column, row parity) ----
+    const int t2 = tid - 32, zc = t2 % n, zp = t2 / n;
+    for (int i = 2; i <= n; ++i) {
+      // row / column i-1 of the growing block become the identity (column i-1 held u^(i-1), consumed)
+      for (int idx = t2; idx < i - 1; idx += 96) { s.a[i - 1][idx] = 0.0; s.a[idx][i - 1] = 0.0; }
+      if (t2 == 0) s.a[i - 1][i - 1] = 1.0;
+      bar_sync(1, 96);
+      if (i < n && s.hh[i] != 0.0) {
+        if (zc < i) {
+          double acc0 = 0.0, acc1 = 0.0;
+          int k = zp;
+          for (; k + 2 < i; k += 4) {
+            acc0 = fma(s.a[k][i], s.a[k][zc], acc0);
+            acc1 = fma(s.a[k + 2][i], s.a[k + 2][zc], acc1);
           }
-          ei = ein; di = din;
+          for (; k < i; k += 2) acc0 = fma(s.a[k][i], s.a[k][zc], acc0);
+          s.part[zp][zc] = acc0 + acc1;
         }
-        s.a[j0][l] = z0;
-        if (has1) s.a[j1][l] = z1;
-        const float pe = -sn * s2 * c3 * el1 * s.e[l] / dl1;
-        el_abs = fabsf(sn * pe);
-        __syncwarp();
-        if (lane == 0) { s.e[l] = sn * pe; s.d[l] = c * pe; }
-        __syncwarp();
-      } while (el_abs > eps * tst1 && iter < 60);
+        bar_sync(1, 96);
+        if (zc < i) {
+          const double g = (s.part[0][zc] + s.part[1][zc]) * s.hinv[i];
+          for (int k = zp; k < i; k += 2) s.a[k][zc] = fma(-g, s.a[k][i], s.a[k][zc]);
+        }
+        bar_sync(1, 96);
+      }
     }
-    __syncwarp();
-    if (lane == 0) { s.d[l] += fsh; s.e[l] = 0.f; }
-    __syncwarp();
+    if (dbg_clk && t2 == 0) dbg_clk[mat * 6 + 3] = clock64();
+    // ---- phase 3 (consumers, warps 1-2): apply the rotation stream to the rows of Z ----
+    if (warp <= 2) {
+      const bool active = t2 < n;
+      const int row = active ? t2 : 0;
+      int cons = 0;
+      for (;;) {
+        const int dn = ld_volatile_s(&s.done);
+        const int pr = ld_volatile_s(&s.produced);
+        __threadfence_block();
+        if (pr == cons) {
+          if (dn) break;
+          __nanosleep(100);
+          continue;
+        }
+        while (cons < pr) {  // whole sweeps are published at once
+          const double2 hd = s.ring[cons & R1];
+          const int l = (int)hd.x, m = (int)hd.y, cnt = m - l;
+          double z = s.a[row][m];
+          int slot = (cons + 1) & R1;
+          for (int k = 0, i = m - 1; k < cnt; ++k, --i) {
+            const double2 cs = s.ring[slot];
+            slot = (slot + 1) & R1;
+            const double y = s.a[row][i];
+            if (active) s.a[row][i + 1] = fma(cs.y, y, cs.x * z);
+            z = fma(cs.x, y, -cs.y * z);
+          }
+          if (active) s.a[row][l] = z;
+          cons += cnt + 1;
+        }
+        __syncwarp();
+        __threadfence_block();
+        if (lane == 0) st_volatile_s(&s.consumed[warp - 1], cons);
+      }
+    }
   }
-
+  __syncthreads();
+  if (tid < n) s.u[tid] = rsqrt(fabs(s.d[tid]));
+  __syncthreads();
   float* out = sv_out + (int64_t)mat * n * n;
-  for (int i = lane; i < n * n; i += 32) {
+  for (int i = tid; i < n * n; i += kEigThreads) {
     const int a = i / n, b = i - a * n;
-    out[i] = round16<BF16>(s.a[a][b] * rsqrtf(fabsf(s.d[b])));
+    out[i] = round16<BF16>((float)(s.a[a][b] * s.u[b]));
+    if (dbg_vec) dbg_vec[(int64_t)mat * n * n + i] = s.a[a][b];
   }
+  if (dbg_lam && tid < n) dbg_lam[(int64_t)mat * n + tid] = s.d[tid];
+  if (dbg_clk && tid == 0) dbg_clk[mat * 6 + 4] = clock64();
 }
 
 // ---- kernel 3: grid (n_chunks, HKV): score_t = round16(sum_j round16(round16(xc_t . sv_j)^2)) ----
@@ -560,25 +713,20 @@ static int leverage_launch(const void* k_pre, int64_t k_stride_n, int64_t k_stri
   wsb += lev_align(mats * kSk * kSk * sizeof(float));
   p.mean = reinterpret_cast<float*>(wsb);
   const size_t smem = sizeof(LevSmem);
-  static bool attr_set = false;
-  if (!attr_set) {
-    CVLLM_CHECK_CUDA(cudaFuncSetAttribute(leverage_gram_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    CVLLM_CHECK_CUDA(cudaFuncSetAttribute(leverage_gram_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    CVLLM_CHECK_CUDA(cudaFuncSetAttribute(leverage_score_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    CVLLM_CHECK_CUDA(cudaFuncSetAttribute(leverage_score_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    CVLLM_CHECK_CUDA(cudaFuncSetAttribute(leverage_eigql_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(QlSmem) * kQlWarps)));
-    CVLLM_CHECK_CUDA(cudaFuncSetAttribute(leverage_eigql_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(QlSmem) * kQlWarps)));
-    attr_set = true;
-  }
+  static std::atomic<uint64_t> attr_g[2] = {{0}, {0}}, attr_s[2] = {{0}, {0}};
   const dim3 grid(n_chunks, HKV);
   if (dtype == CVLLM_BF16) {
+    CVLLM_CHECK_CUDA(ensure_max_dyn_smem((const void*)leverage_gram_kernel<true>, (int)smem, attr_g[1]));
+    CVLLM_CHECK_CUDA(ensure_max_dyn_smem((const void*)leverage_score_kernel<true>, (int)smem, attr_s[1]));
     leverage_gram_kernel<true><<<grid, kLevThreads, smem, st>>>(p);
-    leverage_eigql_kernel<true><<<(unsigned)((mats + kQlWarps - 1) / kQlWarps), kQlWarps * 32, sizeof(QlSmem) * kQlWarps, st>>>(p.gram, p.sv, chunk_offsets, HKV, (int)mats);
+    leverage_eig_kernel<true><<<(unsigned)mats, kEigThreads, 0, st>>>(p.gram, p.sv, chunk_offsets, HKV, (int)mats, nullptr, nullptr, nullptr);
     leverage_score_kernel<true><<<grid, kLevThreads, smem, st>>>(p);
     leverage_finalize_kernel<true><<<n_chunks, 256, 0, st>>>(p.raw, chunk_offsets, out_scores, HKV, normalize);
   } else {
+    CVLLM_CHECK_CUDA(ensure_max_dyn_smem((const void*)leverage_gram_kernel<false>, (int)smem, attr_g[0]));
+    CVLLM_CHECK_CUDA(ensure_max_dyn_smem((const void*)leverage_score_kernel<false>, (int)smem, attr_s[0]));
     leverage_gram_kernel<false><<<grid, kLevThreads, smem, st>>>(p);
-    leverage_eigql_kernel<false><<<(unsigned)((mats + kQlWarps - 1) / kQlWarps), kQlWarps * 32, sizeof(QlSmem) * kQlWarps, st>>>(p.gram, p.sv, chunk_offsets, HKV, (int)mats);
+    leverage_eig_kernel<false><<<(unsigned)mats, kEigThreads, 0, st>>>(p.gram, p.sv, chunk_offsets, HKV, (int)mats, nullptr, nullptr, nullptr);
     leverage_score_kernel<false><<<grid, kLevThreads, smem, st>>>(p);
     leverage_finalize_kernel<false><<<n_chunks, 256, 0, st>>>(p.raw, chunk_offsets, out_scores, HKV, normalize);
   }
@@ -606,4 +754,20 @@ extern "C" int cvllm_leverage_scores_from_sketch(const void* sketch_rows, const 
   if (N > 0 && n_chunks > 0) CVLLM_CHECK_ARG(sketch_rows != nullptr);
   return leverage_launch(nullptr, 0, 0, sketch_rows, chunk_offsets, n_chunks, max_chunk, phi, out_scores, N,
                          HKV, 128, sketch, regularizer, normalize, dtype, workspace, workspace_bytes, stream);
+}
+
+// Test entry (tests/test_gpu_scores.py): the eigensolver alone.  gram: fp32 [mats, 48, 48] symmetric;
+// lam_out: fp64 [mats, 48]; vec_out: fp64 [mats, 48, 48] (columns = eigenvectors, arbitrary order);
+// sv_out: fp32 [mats, 48, 48] = round16(V |lam|^-1/2), the product output.
+extern "C" int cvllm_selftest_eig(const float* gram, double* lam_out, double* vec_out, float* sv_out, int mats,
+                                  int dtype, long long* clk_out, cvllm_stream_t stream) {
+  CVLLM_CHECK_ARG(gram && lam_out && vec_out && sv_out && mats > 0);
+  CVLLM_CHECK_ARG(dtype == CVLLM_F16 || dtype == CVLLM_BF16);
+  auto st = static_cast<cudaStream_t>(stream);
+  if (dtype == CVLLM_BF16)
+    leverage_eig_kernel<true><<<mats, kEigThreads, 0, st>>>(gram, sv_out, nullptr, 1, mats, lam_out, vec_out, clk_out);
+  else
+    leverage_eig_kernel<false><<<mats, kEigThreads, 0, st>>>(gram, sv_out, nullptr, 1, mats, lam_out, vec_out, clk_out);
+  CVLLM_CHECK_LAUNCH();
+  return CVLLM_OK;
 }

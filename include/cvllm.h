@@ -10,7 +10,11 @@
  *     void*) last, launches on it and returns without synchronising
  *   - return value: 0 = launched; negative = argument error detected on the
  *     host before any launch (see CVLLM_E_*); nothing is thrown
- *   - no torch types, no global state (TMA descriptors are rebuilt per call)
+ *   - no torch types; TMA descriptors are rebuilt per call.  Process state is
+ *     limited to: the launch counter, a per-(kernel, device) "dynamic shared
+ *     memory limit raised" bit (so one process can drive several GPUs), a
+ *     per-device SM-count cache, and the explicit test options below.  The
+ *     library never reads the environment.
  *   - all index tensors are int32 unless stated; scores are fp32
  *   - strides are in ELEMENTS of the tensor's dtype
  *   - `dtype`: CVLLM_F16 or CVLLM_BF16 (the arithmetic is always fp32
@@ -50,6 +54,13 @@ const char* cvllm_last_error(void);
 /* Number of kernels this library has launched in this process (monotonic).
  * Lets a caller report how many of its kernels ran inside a timed region. */
 uint64_t cvllm_launch_count(void);
+/* Test / profiling switches (never needed by a product caller; defaults = product behaviour):
+ *   "prefill_v1" 1|0         force the one-query-head-per-CTA prefill kernel (the path odd GQA groups take)
+ *   "prefill_threshold" t    lazy-rescale threshold of the prefill softmax in log2 units (0 exercises the
+ *                            O-correction path on every growing row max); negative = built-in default
+ *   "decode_mode" m          decode_attn.cu profiling modes (0 = product), "decode_slots" n  TMA ring depth cap
+ * Returns CVLLM_E_ARG for an unknown name. */
+int cvllm_set_test_option(const char* name, double value);
 /* Profiling only: in a library built with -DCVLLM_DECODE_TRACE (tools/trace_decode.py) the next decode launches
  * stamp 8 globaltimer values per CTA (entry, lengths read, first unit landed, streaming done, merge done, role,
  * ticket taken, slots folded) into dev_buf (8 * #CTAs uint64); NULL = off.  Returns -1 in the normal build. */
@@ -335,6 +346,15 @@ int cvllm_snapkv_scores(const void* q, const void* k, int64_t q_stride_n,
                         int HKV, int D, int max_seqlen_k, float sm_scale, int kpool,
                         int pool_segment, float* out, int dtype, void* workspace,
                         size_t workspace_bytes, cvllm_stream_t stream);
+
+/* Test entry: the fp64 symmetric eigensolver of the leverage chain alone (csrc/score_leverage.cu).
+ * gram fp32 [mats,48,48]; lam_out fp64 [mats,48]; vec_out fp64 [mats,48,48] (columns = eigenvectors, any
+ * order); sv_out fp32 [mats,48,48] = round16(V |lam|^-1/2), what the score kernel consumes
+ * (reference compression/compactor.py:177,197).  clk_out (optional, int64 [mats,6]): SM clock at kernel entry,
+ * after the tridiagonal reduction, at the end of the QL producer, at the end of the reflector accumulation, at
+ * exit, and the number of ring entries produced (profiling). */
+int cvllm_selftest_eig(const float* gram, double* lam_out, double* vec_out, float* sv_out, int mats,
+                       int dtype, long long* clk_out, cvllm_stream_t stream);
 
 /* ------------------------------------------------------------------------
  * Self tests (device sanity for descriptor encodings; used by tests only)

@@ -2,6 +2,7 @@
 import pytest
 import torch
 
+from compactor_vllm import _native
 from compactor_vllm.attention.sparse_varlen_kernel import causal_sparse_varlen_with_cache
 from oracle import attention as oa
 
@@ -15,15 +16,13 @@ REL = {torch.float16: 2e-3, torch.bfloat16: 1e-2}
 
 
 @pytest.fixture(autouse=True, params=["paired", "single"])
-def kernel_variant(request, monkeypatch):
+def kernel_variant(request):
     """Every test runs on both tcgen05 kernels: 'paired' = two query heads of a KV head per CTA
     (prefill_attn2.cu, the default for even GQA groups), 'single' = one head per CTA (prefill_attn.cu,
-    the path odd groups take), forced through the library's CVLLM_PREFILL_V1 switch."""
-    if request.param == "single":
-        monkeypatch.setenv("CVLLM_PREFILL_V1", "1")
-    else:
-        monkeypatch.delenv("CVLLM_PREFILL_V1", raising=False)
-    return request.param
+    the path odd groups take), forced through the library's "prefill_v1" test option."""
+    _native.set_test_option("prefill_v1", 1 if request.param == "single" else 0)
+    yield request.param
+    _native.set_test_option("prefill_v1", 0)
 
 
 def _run(q, k, v, kc, vc, lens, pt, bm, cu, HKV, PS, scale=None):
@@ -115,11 +114,17 @@ def test_prefill_bf16_16k_single_sequence():
     assert rel_err(out, ref) <= REL[dtype]
 
 
-@pytest.mark.parametrize("threshold", ["0", "8"])
-def test_prefill_correction_path(threshold, monkeypatch):
+@pytest.fixture
+def rescale_threshold():
+    yield lambda t: _native.set_test_option("prefill_threshold", t)
+    _native.set_test_option("prefill_threshold", -1.0)
+
+
+@pytest.mark.parametrize("threshold", [0.0, 8.0])
+def test_prefill_correction_path(threshold, rescale_threshold):
     """A 1-key first tile makes later tiles raise the running max by far more than the lazy-rescale
     threshold, so the O-correction path runs; threshold 0 (test hook) forces it on every increase."""
-    monkeypatch.setenv("CVLLM_PREFILL_THRESHOLD", threshold)
+    rescale_threshold(threshold)
     dtype, HQ, HKV, D, PS = torch.bfloat16, 8, 2, 128, 128
     lens = [[1, 129], [257, 1]]
     kc, vc, pt, bm = make_paged(2, HKV, D, PS, lens, dtype, DEV, seed=13, poison=True)

@@ -116,6 +116,56 @@ def test_snapkv_accumulates_in_place():
 
 
 # ---------------------------------------------------------------------------------- leverage
+def _gram_like(mats, rank, noise, seed, dtype=torch.bfloat16):
+    """fp32 Grams shaped like the chain's: X^T X of a low-rank + noise sketch, rounded entrywise to 16 bit
+    (so possibly indefinite), + 5e-3 I.  |lam| spans ~1e-2 .. 1e5."""
+    g = torch.Generator().manual_seed(seed)
+    X = torch.randn((mats, 512, rank), generator=g) @ (3.0 * torch.randn((mats, rank, 48), generator=g))
+    X = X + noise * torch.randn((mats, 512, 48), generator=g)
+    X = X - X.mean(dim=1, keepdim=True)
+    G = (X.transpose(1, 2) @ X).to(dtype).float()
+    G = torch.triu(G) + torch.triu(G, 1).transpose(1, 2)
+    return G + 5e-3 * torch.eye(48)
+
+
+def test_eigensolver_vs_fp64_eigh():
+    """The fp64 CTA-per-matrix tred2/tql2 (csrc/score_leverage.cu) against torch.linalg.eigh in fp64 on
+    graded, indefinite Gram matrices plus degenerate cases (reg*I, diagonal, a zero row/column block,
+    repeated eigenvalues): eigenvalues to 1e-10 |lam|_max, residual and orthogonality to 1e-9, and the product
+    output round16(V |lam|^-1/2) reproduced from the returned (lam, V)."""
+    from compactor_vllm import _native as N
+    mats = [_gram_like(24, 12, 0.05, 0), _gram_like(8, 3, 1e-3, 1), _gram_like(8, 48, 1.0, 2)]
+    special = torch.zeros((4, 48, 48))
+    special[0] = 5e-3 * torch.eye(48)
+    special[1] = torch.diag(torch.linspace(-3.0, 1e4, 48))
+    special[2] = _gram_like(1, 12, 0.05, 3)[0]
+    special[2][20:30] = 0
+    special[2][:, 20:30] = 0
+    special[2][range(20, 30), range(20, 30)] = 5e-3  # decoupled block: H_i = I steps in the reduction
+    special[3][:24, :24] = _gram_like(1, 6, 0.1, 4)[0][:24, :24]
+    special[3][24:, 24:] = special[3][:24, :24]  # every eigenvalue twice
+    G = torch.cat(mats + [special]).contiguous()
+    M = G.shape[0]
+    Gd = G.to(DEV)
+    lam = torch.empty((M, 48), dtype=torch.float64, device=DEV)
+    vec = torch.empty((M, 48, 48), dtype=torch.float64, device=DEV)
+    sv = torch.empty((M, 48, 48), dtype=torch.float32, device=DEV)
+    N.check(N.lib().cvllm_selftest_eig(N.ptr(Gd), N.ptr(lam), N.ptr(vec), N.ptr(sv), M, N.CVLLM_BF16, None, N.stream()),
+            "cvllm_selftest_eig")
+    torch.cuda.synchronize()
+    lam, vec, sv = lam.cpu(), vec.cpu(), sv.cpu()
+    G64 = G.double()
+    ref = torch.linalg.eigvalsh(G64)
+    scale = ref.abs().max(dim=1).values.clamp_min(1e-300)
+    assert ((lam.sort(dim=1).values - ref).abs().max(dim=1).values / scale).max().item() <= 1e-10
+    resid = (G64 @ vec - vec * lam.unsqueeze(1)).abs().amax(dim=(1, 2)) / scale
+    assert resid.max().item() <= 1e-9, resid.max().item()
+    orth = (vec.transpose(1, 2) @ vec - torch.eye(48, dtype=torch.float64)).abs().amax(dim=(1, 2))
+    assert orth.max().item() <= 1e-9, orth.max().item()
+    want = (vec * lam.abs().rsqrt().unsqueeze(1)).float().to(torch.bfloat16).float()
+    assert torch.equal(sv, want)
+
+
 def _structured_keys(N, H, D, dtype, seed):
     """Low-rank + positional drift + noise: leverage scores with real spread (randn keys make them
     near-uniform)."""

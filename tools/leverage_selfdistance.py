@@ -14,7 +14,11 @@ reference (baseline/_ref), varying only things the reference does not pin:
                  (S = |lambda|): the exact factorisation of what the reference factorises
   ref_ulp        as shipped, K perturbed by one bf16 ulp in 1 % of its entries
   ref_splitk     as shipped, torch.backends.cuda.matmul.allow_bf16_reduced_precision_reduction flipped (another
-                 legal cuBLAS accumulation order for the bf16 GEMMs)
+                 legal cuBLAS accumulation order for the bf16 GEMMs; no effect at these shapes)
+  ref_gram_f32   as shipped, but the Gram X^T X is accumulated by an fp32 GEMM from the same bf16 operands and then
+                 rounded to bf16 — the same sum in another fp32 order: what ANY other GEMM kernel (a different
+                 cuBLAS version / heuristic, or this repo's) is expected to look like
+  ref_sketch_f32 likewise for the sketch GEMM X = K.PHI
   ours / ours_sketch / ours_ulp   this repo (K route, rope.cu sketch route is covered by tests; perturbed K)
 
 Statistics of every variant against `ref`, on the bench's structured keys and on white-noise keys, at 32768
@@ -111,6 +115,18 @@ def run_side(side: str, n_tok: int):
             outs[f"{kind}/ref_eigh64"] = lev(k_pre)
         finally:
             torch.linalg.svd = real_svd
+        real_mm = torch.matmul
+        for tag, is_target in (("gram_f32", lambda a, b: a.shape[-2] == 48 and b.shape[-1] == 48 and a.shape[-1] > 48),
+                               ("sketch_f32", lambda a, b: a.shape[-1] == D and b.shape[-1] == 48)):
+            def mm(a, b, _t=is_target):
+                if a.dtype == torch.bfloat16 and _t(a, b):
+                    return real_mm(a.float(), b.float()).to(torch.bfloat16)
+                return real_mm(a, b)
+            torch.matmul = mm
+            try:
+                outs[f"{kind}/ref_{tag}"] = lev(k_pre)
+            finally:
+                torch.matmul = real_mm
         flag = torch.backends.cuda.matmul.allow_bf16_reduced_precision_reduction
         torch.backends.cuda.matmul.allow_bf16_reduced_precision_reduction = not flag
         try:
