@@ -37,7 +37,8 @@ class PeerAllReduce:
         assert self.world <= 8
         self.device = device or torch.device("cuda", torch.cuda.current_device())
         # One-shot reads (world-1) x message per rank, two-shot 2 x (world-1)/world x message plus one publishing
-        # barrier (a system-scope fence): measured switch points on one 8 x B200 box (profiles/r01h_tp_allreduce_n8.json).
+        # barrier; every barrier is a system-scope release / acquire pair (csrc/allreduce.cu).  Switch points measured
+        # on one 8 x B200 box (profiles/r01h_tp_allreduce_n8.json, re-checked in profiles/r02_tp_allreduce*.json).
         # Measured per call inside a CUDA graph, [rows, 8192] bf16 (profiles/r01h_tp_allreduce*.json):
         #   8 ranks: one-shot 7.8 / 10.6 / 19.2 us at 16 KB / 256 KB / 1 MB, two-shot 11.8 / 13.6 / 14.9 us -> switch
         #            at 512 KB; 4 MB: 21.3 us (NCCL 56.0), 8 MB: 33.5 us (NCCL 73.1)
@@ -86,9 +87,12 @@ class PeerAllReduce:
         assert nbytes <= self.max_bytes
         return self._payload[:nbytes].view(dtype).view(*shape)
 
-    def reduce_staged(self, staged: torch.Tensor) -> torch.Tensor:
-        """Sum over ranks of what each rank put in its staging area (same shape everywhere)."""
-        out = torch.empty(staged.shape, dtype=staged.dtype, device=self.device)
+    def reduce_staged(self, staged: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """Sum over ranks of what each rank put in its staging area (same shape everywhere), written to `out`
+        (a fresh tensor when None; `out` must not alias the staging area)."""
+        if out is None:
+            out = torch.empty(staged.shape, dtype=staged.dtype, device=self.device)
+        assert out.is_contiguous() and out.dtype == staged.dtype and out.numel() == staged.numel()
         if staged.numel() * staged.element_size() >= self.twoshot_min_bytes:
             rc = N.lib().cvllm_allreduce_twoshot(self._bases, self.rank, self.world, N.ptr(out), staged.numel(),
                                                  N.dtype_code(staged.dtype), self.max_bytes, N.stream(self.device))
@@ -100,13 +104,15 @@ class PeerAllReduce:
         return out
 
     def all_reduce(self, t: torch.Tensor) -> torch.Tensor:
-        """Out-of-place sum over ranks; falls to NCCL (in place on a copy-free path) when the message is large."""
-        if not self.fits(t):
+        """`dist.all_reduce(t)` semantics on both routes: `t` holds the sum over ranks afterwards and is returned
+        (the reference's in-place idiom, layers/linear.py:151).  Large or odd-shaped messages go to NCCL; the rest
+        are copied into the shared staging area and summed by the peer-memory kernel straight back into `t`."""
+        if not self.fits(t) or not t.is_contiguous():
             dist.all_reduce(t, group=self.group)
             return t
         st = self.staging(t.shape, t.dtype)
         st.copy_(t)
-        return self.reduce_staged(st)
+        return self.reduce_staged(st, out=t)
 
     def close(self) -> None:
         lib = N.lib()
@@ -132,8 +138,11 @@ class RowParallelLinear(nn.Module):
     def __init__(self, input_size: int, output_size: int, bias: bool = False,
                  peer_all_reduce: Optional[PeerAllReduce] = None):
         super().__init__()
-        self.tp_rank = dist.get_rank() if dist.is_initialized() else 0
-        self.tp_size = dist.get_world_size() if dist.is_initialized() else 1
+        # the tensor-parallel group is the peer all-reduce's group when one is supplied (it may be a subgroup)
+        group = peer_all_reduce.group if peer_all_reduce is not None else None
+        self.tp_group = group
+        self.tp_rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.tp_size = dist.get_world_size(group) if dist.is_initialized() else 1
         assert input_size % self.tp_size == 0
         self.weight = nn.Parameter(torch.empty(output_size, input_size // self.tp_size))
         self.bias = nn.Parameter(torch.empty(output_size)) if bias else None
@@ -153,5 +162,5 @@ class RowParallelLinear(nn.Module):
                 torch.mm(rows, self.weight.t(), out=st)  # the partial lands in the shared buffer: no copy
                 return self.peer.reduce_staged(st).view(out_shape)
         y = F.linear(x, self.weight, bias)
-        dist.all_reduce(y)
+        dist.all_reduce(y, group=self.tp_group)
         return y

@@ -26,17 +26,29 @@ struct ArPeers {
   void* base[kArMaxWorld];  // base[r] = rank r's buffer as mapped in THIS process
 };
 
-// Flag traffic is volatile (relaxed, system-visible), not release / acquire: a release store at system scope costs
-// a MEMBAR.SYS (~3 us per barrier, measured), and neither barrier needs one — the payload a peer reads after the
-// first barrier was written by an EARLIER kernel of the producer's stream (complete at the kernel boundary and
-// served from the owner's L2, the coherence point for NVLink reads); the second barrier only orders loads that
-// have already returned (their values were consumed before the __syncthreads in front of it).
+// Memory model.  Every barrier that GUARDS DATA a peer GPU reads is a system-scope release / acquire pair:
+//   signaller: __syncthreads (block's prior accesses happen-before thread t) -> fence.acq_rel.sys -> st.relaxed.sys flag
+//   waiter   : ld.acquire.sys poll -> __syncthreads -> the block's loads of the peer's data
+// This covers (a) the start barrier: the payload was written by EARLIER kernels of the producer's stream, which the
+// kernel boundary orders before this kernel's fence, so the release is cumulative over it; (b) the two-shot publish
+// barrier: slices written inside this kernel; (c) the end barrier: the peer's loads of my payload are ordered before
+// its flag store by the same fence, and my acquire orders the next call's overwrite after them (write-after-read).
+// The round-1 form (volatile flags, gpu-scope fence on publish only: 1-3 us faster per call, correct on this
+// hardware in every stress run but a data race under the PTX model) is kept behind -DCVLLM_AR_RELAXED_FLAGS for A/B.
 __device__ __forceinline__ void st_flag(uint32_t* p, uint32_t v) {
+#ifdef CVLLM_AR_RELAXED_FLAGS
   asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+#else
+  asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+#endif
 }
 __device__ __forceinline__ uint32_t ld_flag(const uint32_t* p) {
   uint32_t v;
+#ifdef CVLLM_AR_RELAXED_FLAGS
   asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+#else
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+#endif
   return v;
 }
 
@@ -44,40 +56,22 @@ __device__ __forceinline__ uint32_t ld_flag(const uint32_t* p) {
 // calls; ranks run the same launches in the same order, so epochs agree without any host-side counter (a CUDA
 // graph replays the same kernel arguments).  Signal = one remote store of the epoch into the peer's word for
 // (phase, block, me); wait = spin on my own words until they reach it.  A peer can be at most one call ahead,
-// hence the >= comparison.
-// PUBLISH = true: data written by THIS kernel (by any thread of the block, before the leading __syncthreads) must be
-// visible to the peers that see the flag.  The data lives in THIS rank's memory and peers read it with loads that
-// are served by this GPU's L2, so a gpu-scope fence (writes performed at the L2, cumulative over the block's writes
-// through the barrier) in front of the flag store is what is needed; a system-scope fence also waits for every
-// outstanding remote store (+1..3 us per call at 8 ranks, measured).  The 64-call back-to-back stress in
-// tools/tp_allreduce_check.py checks every output bit against the fp32 rank-order sum.  -DCVLLM_AR_SYSFENCE at
-// build time restores the formal .sys fence + acquire poll.
+// hence the >= comparison.  PUBLISH marks the barrier behind which peers read data written by THIS kernel (only
+// the relaxed-flags build treats it differently).
 template <bool PUBLISH = false>
 __device__ __forceinline__ void ar_barrier(const ArPeers& peers, int rank, int world, int phase, uint32_t epoch) {
   __syncthreads();
   if (threadIdx.x < world) {
     const int peer = threadIdx.x;
     const int word = kArBlocks + (phase * kArBlocks + blockIdx.x) * kArMaxWorld;
-#ifdef CVLLM_AR_SYSFENCE
-    if (PUBLISH) __threadfence_system();
-#else
+#ifdef CVLLM_AR_RELAXED_FLAGS
     if (PUBLISH) __threadfence();
+#else
+    asm volatile("fence.acq_rel.sys;" ::: "memory");
 #endif
     st_flag(reinterpret_cast<uint32_t*>(peers.base[peer]) + word + rank, epoch);
     const uint32_t* mine = reinterpret_cast<const uint32_t*>(peers.base[rank]) + word + peer;
-#ifdef CVLLM_AR_SYSFENCE
-    constexpr bool kAcquirePoll = PUBLISH;
-#else
-    constexpr bool kAcquirePoll = false;
-#endif
-    if (kAcquirePoll) {
-      uint32_t v;
-      do {
-        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(mine) : "memory");
-      } while ((int32_t)(v - epoch) < 0);
-    } else {
-      while ((int32_t)(ld_flag(mine) - epoch) < 0) {}
-    }
+    while ((int32_t)(ld_flag(mine) - epoch) < 0) {}
   }
   __syncthreads();
 }

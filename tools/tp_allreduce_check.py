@@ -40,6 +40,17 @@ def main():
     torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)))
     dev = torch.device("cuda", torch.cuda.current_device())
     dist.init_process_group("nccl", device_id=dev)
+    res = run_checks(dev, rank, world, timing=True)
+    if rank == 0:
+        print(json.dumps(res))
+    dist.destroy_process_group()
+    sys.exit(0 if res["ok"] else 1)
+
+
+def run_checks(dev, rank: int, world: int, timing: bool = True) -> dict:
+    """All parity checks (and, with timing=True, the latency tables).  Needs an initialised NCCL process group;
+    bench.py calls it with timing=False inside its --gpus N run so the driver's own launch exercises the
+    multi-rank all-reduce."""
     from compactor_vllm.layers.linear import PeerAllReduce, RowParallelLinear, shard_rows
 
     par = PeerAllReduce(max_bytes=8 << 20, twoshot_min_bytes=1 << 62)  # one-shot only
@@ -73,10 +84,11 @@ def main():
         res["checks"][f"rows{rows}"] = {"bit_exact_vs_fp32_rank_order": exact, "identical_on_all_ranks": identical,
                                         "close_to_fp32": close, "close_to_nccl": near_nccl}
         ok &= exact and identical and close and near_nccl
-        xs = x.clone()
-        res["us"][f"peer_{rows}x8192"] = timed(lambda: par.all_reduce(xs))
-        xn = x.clone()
-        res["us"][f"nccl_{rows}x8192"] = timed(lambda: dist.all_reduce(xn))
+        if timing:
+            xs = x.clone()
+            res["us"][f"peer_{rows}x8192"] = timed(lambda: par.all_reduce(xs))
+            xn = x.clone()
+            res["us"][f"nccl_{rows}x8192"] = timed(lambda: dist.all_reduce(xn))
 
     # ragged slices (15 vectors over `world` ranks) and an empty slice (1 vector)
     for shape in ((3, 40), (1, 8)):
@@ -88,7 +100,7 @@ def main():
     # stress: 64 back-to-back two-shot calls on fresh data (no host sync in between), every output checked against
     # the fp32 rank-order sum — a stale slice (a fence that is too weak) shows up as a bit difference
     xs_all = [torch.randn((96 + 8 * (i % 5), 8192), generator=g, device=dev).bfloat16() for i in range(64)]
-    outs = [par2.all_reduce(xi) for xi in xs_all]
+    outs = [par2.all_reduce(xi.clone()) for xi in xs_all]  # all_reduce is in place (dist.all_reduce semantics)
     stress_ok = True
     for xi, oi in zip(xs_all, outs):
         parts = [torch.empty_like(xi) for _ in range(world)]
@@ -99,6 +111,35 @@ def main():
         stress_ok &= torch.equal(oi, acc.bfloat16())
     res["checks"]["twoshot_stress_64_calls_bit_exact"] = bool(stress_ok)
     ok &= bool(stress_ok)
+
+    # in-place contract on both routes: the argument holds the sum afterwards and is the returned tensor
+    xi = torch.randn((16, 8192), generator=g, device=dev).bfloat16()
+    xc = xi.clone()
+    ret = par.all_reduce(xc)
+    nc = xi.clone()
+    dist.all_reduce(nc)
+    inplace_ok = ret.data_ptr() == xc.data_ptr() and (xc.float() - nc.float()).abs().max().item() <= 4e-2 * nc.float().abs().max().item()
+    res["checks"]["all_reduce_in_place"] = bool(inplace_ok)
+    ok &= bool(inplace_ok)
+
+    # interleaved stress on ONE buffer: message sizes hop across the one-shot / two-shot switch point (and the
+    # block count changes from call to call, so per-block epochs advance unevenly), 96 calls with no host sync
+    par_mix = PeerAllReduce(max_bytes=8 << 20, twoshot_min_bytes=1 << 20)
+    rows_mix = [1, 8, 40, 64, 65, 128, 300, 509, 2, 96, 63, 256]
+    xs_mix = [torch.randn((rows_mix[(7 * i + i // 5) % len(rows_mix)], 8192), generator=g, device=dev).bfloat16()
+              for i in range(96)]
+    outs = [par_mix.all_reduce(xi.clone()) for xi in xs_mix]
+    mix_ok = True
+    for xi, oi in zip(xs_mix, outs):
+        parts = [torch.empty_like(xi) for _ in range(world)]
+        dist.all_gather(parts, xi)
+        acc = torch.zeros(xi.shape, dtype=torch.float32, device=dev)
+        for pp in parts:
+            acc += pp.float()
+        mix_ok &= torch.equal(oi, acc.bfloat16())
+    res["checks"]["interleaved_oneshot_twoshot_stress_96_calls_bit_exact"] = bool(mix_ok)
+    ok &= bool(mix_ok)
+    par_mix.close()
 
     # RowParallelLinear: sharded weight + peer all-reduce == unsharded GEMM (bf16 tolerance)
     gw = torch.Generator(device=dev).manual_seed(7)  # same seed on every rank: the full weight
@@ -131,6 +172,11 @@ def main():
         torch.cuda.synchronize()
         res["checks"]["graph_replay_equals_eager"] = bool(torch.equal(yg, y))
         ok &= res["checks"]["graph_replay_equals_eager"]
+        if not timing:
+            res["ok"] = bool(ok)
+            par.close()
+            par2.close()
+            return res
         res["us"]["graph_gemm_plus_peer_allreduce_16x8192"] = timed(graph.replay)
         lin_nccl = RowParallelLinear(8192, 8192).to(dev).to(torch.bfloat16)
         lin_nccl.weight.copy_(shard_rows(W, rank, world))
@@ -177,10 +223,7 @@ def main():
     res["ok"] = bool(ok)
     par.close()
     par2.close()
-    if rank == 0:
-        print(json.dumps(res))
-    dist.destroy_process_group()
-    sys.exit(0 if ok else 1)
+    return res
 
 
 if __name__ == "__main__":
