@@ -2,9 +2,12 @@
 chunk-local non-causal attention mass (post-RoPE).
 
 Reference: compression/compactor.py:16-599.  The two scorers are single C-ABI
-calls (csrc/score_leverage.cu, csrc/score_chunk_attn.cu): no Python loops over
-chunks, no cuSOLVER — the 48x48 Gram systems are factorised in shared memory
-(x^T (G + reg*I)^-1 x, the quantity the reference's SVD computes, :173-210).
+calls (csrc/score_leverage.cu, csrc/score_attn.cu): no Python loops over chunks,
+no cuSOLVER.  Each chunk's 16-bit 48x48 Gram matrix gets a symmetric
+eigendecomposition in shared memory (fp64 tridiagonal reduction + implicit QL,
+one CTA per matrix) and the score is ||x V |lambda|^-1/2||^2 — what the
+reference's SVD yields, :173-210.  A Cholesky solve is NOT equivalent: the
+rounded Gram of low-rank keys is indefinite.
 """
 from __future__ import annotations
 

@@ -29,7 +29,8 @@ class LLMEngine:
             except Exception:
                 self.tokenizer = None
         if self.tokenizer is not None and config.eos == -1:
-            config.eos = getattr(self.tokenizer, "eos_token_id", -1) or -1
+            eos = getattr(self.tokenizer, "eos_token_id", None)
+            config.eos = -1 if eos is None else int(eos)  # token id 0 is a legitimate EOS
         self.model_runner = ModelRunner(config, **runner_kwargs)
         self.master_model_runner = self.model_runner  # the reference's attribute name
 

@@ -1,14 +1,22 @@
-"""KV cache manager: cache sizing, seq_id -> slot map, wiring into layers.
+"""KV cache manager: how many pages fit, which slot a sequence lives in, and the
+wiring of the per-layer cache views into the attention modules.
 
-Reference: core/memory_manager.py:13-182.  `world_size` comes from the config
-(the reference asks torch.distributed, which forces a process group to exist
-even for one GPU); each tensor-parallel rank owns HKV/tp heads and its own
-cache, so nothing here communicates.
+The reference's class (core/memory_manager.py:13-182) mixes three things in its methods: reading the CUDA
+allocator, two sizing formulas, and slot bookkeeping.  Here they are separate pieces:
+
+* `MemorySnapshot`                 what the device allocator reports right now (the only CUDA reads);
+* `kv_page_budget` / `activation_token_budget`   the two sizing formulas as pure integer functions of a
+  snapshot — they have to give the reference's numbers (same cache size => same page ids => same page
+  tables), and are pinned to the reference's own methods in tests/test_host_logic.py;
+* `SlotMap`                        seq_id -> cache slot, handed out by the paged cache;
+* `KVCacheManager`                 the reference's surface (attribute and method names, return values) on top.
+
+Each tensor-parallel rank owns HKV / tp heads and its own cache, so nothing here communicates.
 """
 from __future__ import annotations
 
 import logging
-from typing import Iterable, List, Optional
+from typing import Dict, Iterable, List, NamedTuple, Optional, Sequence, Tuple
 
 import torch
 import torch.distributed as dist
@@ -18,130 +26,144 @@ from torch import nn
 
 logger = logging.getLogger(__name__)
 
+_INT32 = 4
+_SAFETY = 0.9        # fraction of the user's memory fraction the cache may take (reference :97)
+_ACT_SAFETY = 0.95   # same for the activation budget (reference :152)
 
-def _world_size(config: LLMConfig) -> int:
-    if dist.is_available() and dist.is_initialized():
-        return dist.get_world_size()
-    return config.tensor_parallel_size
+
+class MemorySnapshot(NamedTuple):
+    total: int      # device memory
+    free: int       # cudaMemGetInfo free
+    peak: int       # torch allocator, allocated_bytes.all.peak
+    current: int    # torch allocator, allocated_bytes.all.current
+
+    @classmethod
+    def capture(cls, device=None) -> "MemorySnapshot":
+        free, total = torch.cuda.mem_get_info(device)
+        stats = torch.cuda.memory_stats(device)
+        return cls(int(total), int(free), int(stats.get("allocated_bytes.all.peak", 0)),
+                   int(stats.get("allocated_bytes.all.current", 0)))
+
+    @property
+    def used(self) -> int:
+        return self.total - self.free
+
+    @property
+    def transient(self) -> int:
+        """Bytes the forward pass needed on top of what is allocated now (peak - current)."""
+        return self.peak - self.current
+
+
+def table_bytes(num_layers: int, max_batches: int, heads: int, logical_pages: int) -> int:
+    """page_table [L, B, H, P] + bh_seq_lens [L, B, H], int32 (reference :106-114)."""
+    return num_layers * max_batches * heads * (logical_pages + 1) * _INT32
+
+
+def kv_page_budget(snap: MemorySnapshot, frac: float, *, num_layers: int, heads: int, head_dim: int,
+                   page_size: int, elem_size: int, max_batches: int, logical_pages: int) -> int:
+    """Pages per layer that fit: (total * frac * 0.9 - used - transient - tables) // bytes of one page in
+    every layer (K and V).  Reference :92-126; raises RuntimeError where it does."""
+    budget = int(snap.total * frac * _SAFETY) - snap.used - snap.transient
+    if budget <= 0:
+        raise RuntimeError(f"Insufficient memory for KV cache: gpu_memory_utilization={frac:.2f} leaves "
+                           f"{budget} bytes after {snap.used} used and {snap.transient} transient")
+    net = budget - table_bytes(num_layers, max_batches, heads, logical_pages)
+    if net <= 0:
+        raise RuntimeError(f"page-table footprint exceeds KV cache budget ({budget} bytes): reduce max_num_seqs "
+                           f"({max_batches}) or raise gpu_memory_utilization ({frac:.2f})")
+    return max(1, net // (num_layers * 2 * page_size * head_dim * elem_size))
+
+
+def activation_token_budget(snap: MemorySnapshot, frac: float, *, warmup_tokens: int, used_before: int,
+                            peak_after: int, num_pages: int, page_size: int, heads: int) -> int:
+    """Tokens one step may carry: bounded by activations (bytes per token measured on the warm-up pass against
+    what is left of the memory fraction) and by what the cache can hold, both rounded down to whole pages
+    (reference :128-161)."""
+    assert warmup_tokens > 0, "warmup_tokens must be > 0"
+    per_token = max(1, -(-max(0, int(peak_after) - int(used_before)) // warmup_tokens))
+    room = max(0, int(snap.total * frac) - snap.used - max(0, snap.transient))
+    whole_pages = lambda tokens: tokens // page_size * page_size  # noqa: E731
+    return min(whole_pages(num_pages * page_size // heads), whole_pages(int(room * _ACT_SAFETY) // per_token))
+
+
+class SlotMap:
+    """seq_id -> cache slot.  Slots come from (and go back to) the paged cache's free list."""
+
+    def __init__(self):
+        self.by_seq: Dict[int, int] = {}
+
+    def acquire(self, cache: PagedKVCache, seq_id: int) -> Optional[int]:
+        slot = self.by_seq.get(seq_id)
+        if slot is None:
+            slot = cache.new_batch()
+            if slot is None:
+                return None
+            self.by_seq[seq_id] = slot = int(slot)
+        return slot
+
+    def release(self, cache: PagedKVCache, seq_id: int) -> None:
+        cache.free_batch(self.by_seq.pop(seq_id, None))
 
 
 class KVCacheManager:
     def __init__(self, rank: int, config: LLMConfig):
         hf = config.hf_config
-        self.rank = rank
+        tp = dist.get_world_size() if dist.is_available() and dist.is_initialized() else config.tensor_parallel_size
+        assert hf.num_key_value_heads % tp == 0, "world size needs to divide num_kv_heads"
+        self.rank, self.world_size = rank, config.tensor_parallel_size
         self.gpu_frac = config.gpu_memory_utilization
         self.page_size = config.kvcache_page_size
-        self.world_size = config.tensor_parallel_size
-        self.max_num_batches = config.max_num_seqs
-        self.max_model_len = config.max_model_len
-        self.num_layers = hf.num_hidden_layers
-        self.model_dtype = hf.torch_dtype
+        self.max_num_batches, self.max_model_len = config.max_num_seqs, config.max_model_len
+        self.num_layers, self.model_dtype = hf.num_hidden_layers, hf.torch_dtype
         self.head_dim = getattr(hf, "head_dim", None)
-        self.max_pages_per_batch = (self.max_model_len + self.page_size - 1) // self.page_size
-        ws = _world_size(config)
-        assert hf.num_key_value_heads % ws == 0, "world size needs to divide num_kv_heads"
-        self.num_kv_heads = hf.num_key_value_heads // ws
-        self.num_pages = None
+        self.num_kv_heads = hf.num_key_value_heads // tp          # this rank's shard (reference :29-32)
+        self.max_pages_per_batch = -(-self.max_model_len // self.page_size)
+        self.num_pages: Optional[int] = None
         self.paged_cache: Optional[PagedKVCache] = None
-        self.max_batched_tokens = None
-        self.seq_id_to_batch = {}
+        self.max_batched_tokens: Optional[int] = None
+        self._slots = SlotMap()
 
-    def allocate_sequences(self, seq_ids: List[int], max_positions: List[int]):
-        """(ok, batch_mapping) — reference :40-60."""
-        mapping = []
-        for seq_id, want in zip(seq_ids, max_positions):
-            if seq_id not in self.seq_id_to_batch:
-                slot = self.paged_cache.new_batch()
-                if slot is None:
-                    logger.warning("Failed to allocate batch!")
-                    return False, None
-                self.seq_id_to_batch[seq_id] = int(slot)
-            slot = self.seq_id_to_batch[seq_id]
-            mapping.append(slot)
-            status = self.paged_cache.reserve_tokens(slot, want)
-            if status != KVAllocationStatus.SUCCESS:
-                logger.warning(f"Failed to allocate pages ({status})!")
-                return False, None
-        dev = self.paged_cache.page_table.device
-        return True, torch.as_tensor(mapping, dtype=torch.int32, device=dev)
+    # the reference exposes the dict itself (model_runner reads it)
+    @property
+    def seq_id_to_batch(self) -> Dict[int, int]:
+        return self._slots.by_seq
 
-    def free_sequences(self, seq_ids: Iterable[int]):
-        for seq_id in seq_ids:
-            slot = self.seq_id_to_batch.pop(seq_id, None)
-            self.paged_cache.free_batch(slot)
-
-    def init_cache(self, model: nn.Module, num_pages: Optional[int] = None, device_allocator: bool = False):
-        """Size and allocate the cache, then wire it into every attention layer (:67-90).
-        device_allocator=True: the GPU-resident page allocator (same surface, same page ids)."""
-        self.num_pages = (
-            int(num_pages) if num_pages is not None
-            else self.get_num_pages(self.gpu_frac, self.max_pages_per_batch)
-        )
-        self.paged_cache = (DevicePagedKVCache if device_allocator else PagedKVCache)(
-            num_layers=self.num_layers,
-            H_kv=self.num_kv_heads,
-            head_dim=self.head_dim,
-            page_size=self.page_size,
-            num_pages=int(self.num_pages),
-            max_num_batches=self.max_num_batches,
-            device=f"cuda:{self.rank}",
-            dtype=self.model_dtype,
-            max_logical_pages_per_head=int(self.max_pages_per_batch),
-        )
-        self._assign_cache_to_layers(model)
-
-    def _assign_cache_to_layers(self, model) -> None:
-        for layer_index, layer in enumerate(model.model.layers):
-            attn = layer.self_attn.attn
-            k, v, pt, bh = self.paged_cache.layer_slices(layer_index)
-            attn.k_cache, attn.v_cache = k, v
-            attn.page_table, attn.bh_seq_lens = pt, bh
-            attn.page_size = self.page_size
+    # ---- sizing ---------------------------------------------------------------------------------
+    def _shape(self) -> dict:
+        return dict(num_layers=self.num_layers, heads=self.num_kv_heads, head_dim=self.head_dim,
+                    page_size=self.page_size, elem_size=torch.empty((), dtype=self.model_dtype).element_size(),
+                    max_batches=self.max_num_batches)
 
     def page_table_bytes(self, n_logical_pages_max: int) -> int:
-        per_layer = self.max_num_batches * self.num_kv_heads * (n_logical_pages_max + 1) * 4
-        return self.num_layers * per_layer
+        return table_bytes(self.num_layers, self.max_num_batches, self.num_kv_heads, n_logical_pages_max)
 
     def get_num_pages(self, frac: float, n_logical_pages_max: int) -> int:
-        """(total*frac*0.9 - used - peak + current - page_table_bytes) / bytes_per_page (:92-126)."""
-        free, total = torch.cuda.mem_get_info()
-        stats = torch.cuda.memory_stats()
-        peak = int(stats["allocated_bytes.all.peak"])
-        current = int(stats["allocated_bytes.all.current"])
-        budget = int(total * frac * 0.9) - (total - free) - peak + current
-        if budget <= 0:
-            raise RuntimeError(
-                "Insufficient memory for KV cache."
-                f"Try increasing gpu_memory_utilization (currently {frac:.2f})."
-            )
-        net = budget - self.page_table_bytes(n_logical_pages_max)
-        if net <= 0:
-            raise RuntimeError(
-                "page-table footprint exceeds KV cache budget. "
-                f"reduce max_num_seqs ({self.max_num_batches}) "
-                f"or increase kv_cache_mem_fraction (currently {frac:.2f})."
-            )
-        elem = torch.empty((), dtype=self.model_dtype).element_size()
-        per_page = self.num_layers * 2 * self.page_size * self.head_dim * elem
-        return max(1, net // per_page)
+        return kv_page_budget(MemorySnapshot.capture(), frac, logical_pages=n_logical_pages_max, **self._shape())
 
-    def estimate_max_batched_tokens(
-        self, warmup_tokens: int, bytes_used_before_warmup: int, bytes_peak_after_warmup: int
-    ) -> int:
-        """Activation-bound token budget (:128-161)."""
-        assert warmup_tokens > 0, "warmup_tokens must be > 0"
-        delta = max(0, int(bytes_peak_after_warmup) - int(bytes_used_before_warmup))
-        per_token = max(1, (delta + warmup_tokens - 1) // warmup_tokens)
-        free, total = torch.cuda.mem_get_info()
-        stats = torch.cuda.memory_stats()
-        cushion = max(
-            0, int(stats.get("allocated_bytes.all.peak", 0)) - int(stats.get("allocated_bytes.all.current", 0))
-        )
-        act_budget = int(max(0, int(total * self.gpu_frac) - int(total - free) - cushion) * 0.95)
-        by_act = (act_budget // per_token) // self.page_size * self.page_size
-        by_cache = ((self.num_pages * self.page_size) // self.num_kv_heads) // self.page_size * self.page_size
-        self.max_batched_tokens = min(by_cache, by_act)
+    def estimate_max_batched_tokens(self, warmup_tokens: int, bytes_used_before_warmup: int,
+                                    bytes_peak_after_warmup: int) -> int:
+        self.max_batched_tokens = activation_token_budget(
+            MemorySnapshot.capture(), self.gpu_frac, warmup_tokens=warmup_tokens,
+            used_before=bytes_used_before_warmup, peak_after=bytes_peak_after_warmup,
+            num_pages=self.num_pages, page_size=self.page_size, heads=self.num_kv_heads)
         return self.max_batched_tokens
+
+    # ---- the cache ------------------------------------------------------------------------------
+    def init_cache(self, model: nn.Module, num_pages: Optional[int] = None, device_allocator: bool = False):
+        """Size the cache (unless `num_pages` is given), allocate it and hand every attention layer its views.
+        device_allocator=True: the GPU-resident page allocator (same surface, same page ids; SURVEY 8(f)-2)."""
+        if num_pages is None:
+            num_pages = self.get_num_pages(self.gpu_frac, self.max_pages_per_batch)
+        self.num_pages = int(num_pages)
+        cache_type = DevicePagedKVCache if device_allocator else PagedKVCache
+        self.paged_cache = cache_type(
+            num_layers=self.num_layers, max_logical_pages_per_head=int(self.max_pages_per_batch),
+            num_pages=self.num_pages, page_size=self.page_size, H_kv=self.num_kv_heads, head_dim=self.head_dim,
+            max_num_batches=self.max_num_batches, dtype=self.model_dtype, device=f"cuda:{self.rank}")
+        for index, layer in enumerate(model.model.layers):
+            attn = layer.self_attn.attn
+            attn.k_cache, attn.v_cache, attn.page_table, attn.bh_seq_lens = self.paged_cache.layer_slices(index)
+            attn.page_size = self.page_size
 
     @property
     def num_free_batches(self) -> int:
@@ -149,12 +171,37 @@ class KVCacheManager:
 
     @property
     def num_free_pages(self) -> int:
-        if isinstance(self.paged_cache, DevicePagedKVCache):
-            return int(self.paged_cache.free_count.min())
-        return min(len(fp) for fp in self.paged_cache.free_pages)
+        """Free pages of the fullest layer (layers fill unevenly after compression)."""
+        cache = self.paged_cache
+        if isinstance(cache, DevicePagedKVCache):
+            return int(cache.free_count.min())
+        return min(map(len, cache.free_pages))
+
+    # ---- sequences ------------------------------------------------------------------------------
+    def allocate_sequences(self, seq_ids: Sequence[int], max_positions: Sequence[int]
+                           ) -> Tuple[bool, Optional[torch.Tensor]]:
+        """Give every sequence a slot (a new one the first time it is seen) and room for `max_positions[i]`
+        more tokens.  Returns (True, int32 slot vector on the cache's device), or (False, None) as soon as the
+        cache runs out of slots or pages; like the reference (:40-60) what was granted before the failure stays
+        with its sequence — the scheduler retries or frees."""
+        slots: List[int] = []
+        for seq_id, tokens in zip(seq_ids, max_positions):
+            slot = self._slots.acquire(self.paged_cache, seq_id)
+            if slot is None:
+                logger.warning("no free cache slot for sequence %s", seq_id)
+                return False, None
+            status = self.paged_cache.reserve_tokens(slot, tokens)
+            if status != KVAllocationStatus.SUCCESS:
+                logger.warning("no room for %d tokens of sequence %s: %s", tokens, seq_id, status)
+                return False, None
+            slots.append(slot)
+        return True, torch.tensor(slots, dtype=torch.int32, device=self.paged_cache.page_table.device)
+
+    def free_sequences(self, seq_ids: Iterable[int]) -> None:
+        for seq_id in seq_ids:
+            self._slots.release(self.paged_cache, seq_id)
 
     def reclaim_pages(self, seq_ids_to_reclaim: Iterable[int], future_reserved_buffer) -> int:
-        freed = 0
-        for i, seq_id in enumerate(seq_ids_to_reclaim):
-            freed += self.paged_cache.reclaim_pages(self.seq_id_to_batch[seq_id], future_reserved_buffer[i])
-        return freed
+        """Return the pages each sequence holds beyond len + future_reserved_buffer[i] tokens; approximate bytes."""
+        return sum(self.paged_cache.reclaim_pages(self._slots.by_seq[seq_id], future_reserved_buffer[i])
+                   for i, seq_id in enumerate(seq_ids_to_reclaim))

@@ -34,6 +34,10 @@ def _pad_batch(n: int) -> int:
     return b
 
 
+class KVCacheExhausted(RuntimeError):
+    """The paged cache cannot hold the tokens a decode wave may still produce."""
+
+
 class ModelRunner:
     def __init__(self, config: LLMConfig, *, num_pages: Optional[int] = None, seed: int = 0,
                  device_allocator: bool = True, max_batched_tokens: Optional[int] = None):
@@ -162,8 +166,14 @@ class ModelRunner:
         # scheduler step on the host; `DevicePagedKVCache.reserve_tokens_device` is the in-graph alternative)
         for s in live:
             left = s.sampling_params.max_new_tokens - s.num_generated_tokens
-            ok, _ = self.kv.allocate_sequences([s.seq_id], [max(left, 0) + 1])
-            assert ok, "KV cache exhausted (no preemption in the engine shell)"
+            # never ask for more than the model length allows (generation stops there, see _accept): the tail
+            # would be refused as "too long" although those tokens are never produced
+            room = self.config.max_model_len - (s.num_prompt_tokens + s.num_generated_tokens)
+            want = max(min(left, room), 0) + 1
+            ok, _ = self.kv.allocate_sequences([s.seq_id], [want])
+            if not ok:
+                raise KVCacheExhausted(f"sequence {s.seq_id}: no room for {want} more tokens "
+                                       f"({self.kv.num_free_pages} free pages; the engine shell has no preemption)")
         bs = _pad_batch(len(live))
         slots = [self.kv.seq_id_to_batch[s.seq_id] for s in live]
         bm = torch.full((bs,), RESERVED_BATCH, dtype=torch.int32, device=dev)
@@ -197,7 +207,8 @@ class ModelRunner:
 
     def _accept(self, s: Sequence, token: int) -> None:
         s.add_new_token(token)
-        if s.num_generated_tokens >= s.sampling_params.max_new_tokens or token == self.eos:
+        full = s.num_prompt_tokens + s.num_generated_tokens >= self.config.max_model_len  # RoPE table / reservation
+        if s.num_generated_tokens >= s.sampling_params.max_new_tokens or token == self.eos or full:
             s.status = SequenceStatus.FINISHED
 
     # ----------------------------------------------------------------- generate

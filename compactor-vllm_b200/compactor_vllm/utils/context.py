@@ -7,7 +7,7 @@ field names), built from one field table so the two stay in step.
 """
 from __future__ import annotations
 
-from types import SimpleNamespace
+import dataclasses
 from typing import Any
 
 from compactor_vllm.api_types import CompressionMethod
@@ -40,28 +40,19 @@ _STEP_FIELDS: dict[str, Any] = {
 }
 
 
-class _Record(SimpleNamespace):
-    _fields: dict[str, Any] = {}
-
-    def __init__(self, *args, **kwargs):
-        names = list(self._fields)
-        if len(args) > len(names):
-            raise TypeError(f"{type(self).__name__} takes at most {len(names)} positional arguments")
-        values = dict(self._fields)
-        values.update(zip(names, args))
-        for key, val in kwargs.items():
-            if key not in values:
-                raise TypeError(f"{type(self).__name__} has no field {key!r}")
-            values[key] = val
-        super().__init__(**values)
+def _record_type(name: str, table: dict[str, Any], doc: str):
+    """A real dataclass (so `dataclasses.replace / asdict / fields` work as on the reference's classes,
+    utils/context.py:10-40) generated from a field table: every field optional, positional order = table order."""
+    cls = dataclasses.make_dataclass(name, [(key, Any, dataclasses.field(default=default))
+                                            for key, default in table.items()])
+    cls.__doc__ = doc
+    cls.__module__ = __name__
+    return cls
 
 
-class CompressionContext(_Record):
-    _fields = _COMPRESSION_FIELDS
-
-
-class Context(_Record):
-    _fields = _STEP_FIELDS
+CompressionContext = _record_type("CompressionContext", _COMPRESSION_FIELDS,
+                                  "Per-step compression arguments (reference utils/context.py:10-22).")
+Context = _record_type("Context", _STEP_FIELDS, "Per-step attention state (reference utils/context.py:25-40).")
 
 
 _current = Context()

@@ -29,6 +29,16 @@ struct PagePlan {            // workspace layout
 
 __device__ __forceinline__ int pg_cdiv(int a, int b) { return (a + b - 1) / b; }
 
+// A slot named twice in one call is served once (its first occurrence): the second reserve of the same tokens
+// is a no-op on the host allocator too, and counting its pages twice would desynchronise free_count from the
+// bitmap.  nb is a decode batch (<= a few hundred), so the scan is cheaper than a visited table.
+__device__ __forceinline__ bool pg_first_occurrence(const int32_t* __restrict__ slots, int i) {
+  const int b = slots[i];
+  for (int j = 0; j < i; ++j)
+    if (slots[j] == b) return false;
+  return true;
+}
+
 __global__ void __launch_bounds__(kPgThreads) pages_plan_kernel(
     const int32_t* __restrict__ free_count, const int32_t* __restrict__ bh_seq_lens,
     const int32_t* __restrict__ bh_num_pages, const int32_t* __restrict__ slots, int nb, int add_tokens,
@@ -42,7 +52,7 @@ __global__ void __launch_bounds__(kPgThreads) pages_plan_kernel(
   __syncthreads();
   for (int i = 0; i < nb; ++i) {
     const int b = slots[i];
-    const bool live = b != reserved && b >= 0 && b < Bs;
+    const bool live = b != reserved && b >= 0 && b < Bs && pg_first_occurrence(slots, i);
     if (tid == 0) { s_short = 0; s_over = 0; }
     for (int l = tid; l < L; l += kPgThreads) need[l] = 0;
     __syncthreads();
@@ -154,7 +164,7 @@ __global__ void __launch_bounds__(kPgThreads) pages_give_kernel(
   for (int e = tid; e < nb * H; e += kPgThreads) {
     const int i = e / H, h = e - i * H;
     const int b = slots[i];
-    if (b == reserved || b < 0 || b >= Bs) continue;
+    if (b == reserved || b < 0 || b >= Bs || !pg_first_occurrence(slots, i)) continue;
     const int64_t o = ((int64_t)l * Bs + b) * H + h;
     const int alloc = bh_num_pages[o];
     const int used = free_all ? 0 : min(pg_cdiv(bh_seq_lens[o] + future_tokens, PS), alloc);

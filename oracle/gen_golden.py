@@ -439,10 +439,67 @@ def gen_allocator():
         torch.tensor, torch.empty = real_tensor, real_empty
 
 
+def gen_num_splits():
+    """The reference's own `num_splits_heuristic` (attention/sparse_decode_kernel.py:168-192) over a grid of
+    (b x kv-head blocks, context, SM count, split cap): the split count its engine fixes at graph-capture time."""
+    from compactor_vllm.attention.sparse_decode_kernel import num_splits_heuristic
+    rows = []
+    for sms in (108, 132, 148):
+        for max_splits in (1, 4, 16, 64, 256):
+            for blocks in (1, 2, 7, 8, 16, 24, 64, 100, 117, 118, 119, 128, 148, 512):
+                for seq in (1, 512, 1024, 1025, 2048, 4097, 8192, 16344, 32768, 40960, 131072):
+                    rows.append((blocks, seq, sms, max_splits, num_splits_heuristic(blocks, seq, sms, max_splits)))
+    save("num_splits", table=torch.tensor(rows, dtype=torch.int64))
+
+
+def gen_memory_budget():
+    """The reference's KVCacheManager sizing methods (core/memory_manager.py:92-161) evaluated on scripted allocator
+    readings: torch.cuda.mem_get_info / memory_stats are replaced by the scripted values, nothing else is touched."""
+    from compactor_vllm.core import memory_manager as mm
+
+    GB = 1 << 30
+    rows_pages, rows_tokens = [], []
+    real_info, real_stats = torch.cuda.mem_get_info, torch.cuda.memory_stats
+    try:
+        for total in (80 * GB, 180 * GB + 12345):
+            for used in (17 * GB + 999, 30 * GB, 150 * GB):
+                for peak, current in ((20 * GB, 16 * GB + 7), (5 * GB, 5 * GB)):
+                    for frac in (0.5, 0.9, 0.95):
+                        for layers, heads, hd, ps, esz, nb, mlen in ((32, 8, 128, 128, 2, 64, 40960),
+                                                                    (80, 1, 128, 256, 2, 256, 131072),
+                                                                    (36, 4, 64, 128, 4, 8, 4096)):
+                            torch.cuda.mem_get_info = lambda *a, **k: (total - used, total)
+                            torch.cuda.memory_stats = lambda *a, **k: {"allocated_bytes.all.peak": peak,
+                                                                       "allocated_bytes.all.current": current}
+                            m = object.__new__(mm.KVCacheManager)
+                            m.gpu_frac, m.page_size, m.max_num_batches, m.num_layers = frac, ps, nb, layers
+                            m.model_dtype = torch.float32 if esz == 4 else torch.bfloat16
+                            m.head_dim, m.num_kv_heads = hd, heads
+                            nlp = (mlen + ps - 1) // ps
+                            try:
+                                pages = int(m.get_num_pages(frac, nlp))
+                            except RuntimeError:
+                                pages = -1
+                            rows_pages.append((total, used, peak, current, int(frac * 100), layers, heads, hd, ps,
+                                               esz, nb, nlp, pages))
+                            if pages > 0:
+                                m.num_pages = pages
+                                for wt, before, after in ((8192, 16 * GB, 19 * GB + 5), (1000, 4 * GB, 3 * GB)):
+                                    tok = int(m.estimate_max_batched_tokens(wt, before, after))
+                                    rows_tokens.append((total, used, peak, current, int(frac * 100), heads, ps,
+                                                        pages, wt, before, after, tok))
+    finally:
+        torch.cuda.mem_get_info, torch.cuda.memory_stats = real_info, real_stats
+    save("memory_budget", pages=torch.tensor(rows_pages, dtype=torch.int64),
+         tokens=torch.tensor(rows_tokens, dtype=torch.int64))
+
+
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["prefill", "decode", "stores", "chunk", "snapkv", "leverage", "prepath", "allocator"]
+    which = sys.argv[1:] or ["prefill", "decode", "stores", "chunk", "snapkv", "leverage", "prepath", "allocator",
+                             "splits", "memory"]
     table = {"prefill": gen_prefill, "decode": gen_decode, "stores": gen_stores,
              "chunk": gen_chunk_scores, "snapkv": gen_snapkv, "leverage": gen_leverage,
-             "prepath": gen_prepath, "allocator": gen_allocator}
+             "prepath": gen_prepath, "allocator": gen_allocator, "splits": gen_num_splits,
+             "memory": gen_memory_budget}
     for w in which:
         table[w]()

@@ -127,6 +127,34 @@ def test_batched_device_reserve_equals_sequential_host_and_skips_reserved_slot()
     assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]) and a[3] == b[3]
 
 
+def test_repeated_slot_in_one_call_is_served_once():
+    """A slot named twice in one batched reserve / reclaim behaves like two sequential host calls (the second is a
+    no-op): free_count stays equal to the bitmap's popcount and no garbage page id reaches the page table."""
+    cls = _classes()
+    shape = dict(num_layers=2, max_logical_pages_per_head=8, num_pages=64, page_size=16, H_kv=4, head_dim=16,
+                 max_num_batches=4)
+    host = cls["host"](dtype=torch.float16, device=DEV, **shape)
+    dev = cls["device"](dtype=torch.float16, device=DEV, **shape)
+    a, b = host.new_batch(), host.new_batch()
+    assert (a, b) == (dev.new_batch(), dev.new_batch())
+    order = [a, b, a, a, b]
+    for s in order:
+        assert host.reserve_tokens(s, 40).name == "SUCCESS"
+    st = dev.reserve_tokens_device(torch.tensor(order, dtype=torch.int32, device=DEV), 40)
+    assert st.tolist() == [0] * 5
+    x, y = _state(host), _state(dev)
+    assert np.array_equal(x[0], y[0]) and np.array_equal(x[1], y[1]) and x[3] == y[3]
+    assert dev.free_count.tolist() == [len(f) for f in y[3]]
+    for c in (host, dev):
+        c.bh_seq_lens[:, a] = 5
+    for s in (a, a):
+        host.reclaim_pages(s, 0)
+    dev.reclaim_pages_device(torch.tensor([a, a], dtype=torch.int32, device=DEV), 0)
+    x, y = _state(host), _state(dev)
+    assert np.array_equal(x[0], y[0]) and np.array_equal(x[1], y[1]) and x[3] == y[3]
+    assert dev.free_count.tolist() == [len(f) for f in y[3]]
+
+
 def test_decode_reservation_in_a_cuda_graph():
     """reserve 1 token for the running slots + `bh_seq_lens += 1`, captured once and replayed: pages grow
     exactly as the host allocator's would, with no host sync inside the step."""

@@ -222,8 +222,10 @@ def test_config3_qwen8b_snapkv_25pct_40k_batch16_decode():
         eng.bm, eng.lens = all_bm[b:b + 1], [N]
         eng.cu = torch.tensor([0, N], dtype=torch.int32, device=DEV)
         slots, eng.slots = eng.slots, [eng.slots[b]]
-        out, scores = eng.prefill(q, k, v, None, CompressionMethod.SNAPKV, 0.25, 0, w)
-        assert eng.retain == [81856]
+        # the engine's default protected counts (16 / 64) size the budget (utils/arguments.py:109-121 ->
+        # SURVEY's 81760 pairs); SnapKV itself force-keeps only its 32-key observation window (snapkv.py:27-35)
+        out, scores = eng.prefill(q, k, v, None, CompressionMethod.SNAPKV, 0.25, 16, 64)
+        assert eng.retain == [81760]
         if b in (0, B - 1):  # full eviction check on two sequences (a few seconds of oracle each)
             rows = [0, 4096, 20479, 40959]
             assert rel_err(out[rows], _ref_rows(q, k, v, rows, HKV, 1.0 / math.sqrt(D))) < 2e-2
@@ -233,7 +235,7 @@ def test_config3_qwen8b_snapkv_25pct_40k_batch16_decode():
         eng.slots = slots
         del q, k, v, out, scores
     eng.bm, eng.cu, eng.lens = all_bm, all_cu, all_lens
-    assert (lens_bh % PS == 0).all() and int(lens_bh.sum()) >= B * 81856
+    assert (lens_bh % PS == 0).all() and int(lens_bh.sum()) >= B * 81760
     _decode_steps(eng, lens_bh, 4, seed=33, check_every=3)
 
 

@@ -86,7 +86,7 @@ def test_device_restatement_matches_cpu_oracle():
 
 
 # the reference's own grid (tests/test_triton_attention.py:33-50,200-287): fp16, PS=256, HQ=32, HKV=8
-@pytest.mark.parametrize("B", [1, 3])
+@pytest.mark.parametrize("B", [1, 2, 3, 8])
 @pytest.mark.parametrize("cache_len", [0, 1, 70, 128, 8193])
 @pytest.mark.parametrize("append_len", [1, 2, 13, 8000])
 def test_prefill_reference_grid(B, cache_len, append_len):
