@@ -15,3 +15,12 @@ k_pre[:, h].contiguous().cpu().view(torch.int16).numpy().tofile("/tmp/sk_k.bin")
 phi.cpu().view(torch.int16).numpy().tofile("/tmp/sk_phi.bin")
 X[h].contiguous().cpu().view(torch.int16).numpy().tofile("/tmp/sk_x.bin")
 print("wrote", X.shape)
+# which kernel does cuBLAS run for this GEMM?  (name hints at the instruction family: nvjet / sm100 = tcgen05, sm80/sm90 = mma.sync / wgmma)
+from torch.profiler import ProfilerActivity, profile
+with profile(activities=[ProfilerActivity.CUDA]) as prof:
+    torch.matmul(k_pre.transpose(0, 1), phi)
+    ch = X.view(8, -1, 512, 48).clone()
+    torch.matmul(ch.transpose(-1, -2), ch)
+    torch.cuda.synchronize()
+for e in prof.key_averages():
+    print("kernel:", e.key[:160])
