@@ -71,7 +71,11 @@ __device__ __forceinline__ void ar_barrier(const ArPeers& peers, int rank, int w
 #endif
     st_flag(reinterpret_cast<uint32_t*>(peers.base[peer]) + word + rank, epoch);
     const uint32_t* mine = reinterpret_cast<const uint32_t*>(peers.base[rank]) + word + peer;
-    while ((int32_t)(ld_flag(mine) - epoch) < 0) {}
+    // bounded: a peer that never arrives (crashed rank, mismatched launch order) traps this context after ~1 min
+    // of polling instead of hanging the GPU until the driver's watchdog
+    uint32_t spins = 0;
+    while ((int32_t)(ld_flag(mine) - epoch) < 0)
+      if (++spins > (1u << 27)) __trap();
   }
   __syncthreads();
 }
