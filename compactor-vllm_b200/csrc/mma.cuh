@@ -69,4 +69,20 @@ __device__ __forceinline__ void bfrag_regs(const uint4& chunk, int ks, uint32_t&
   b1 = (ks & 1) ? chunk.w : chunk.y;
 }
 
+// "Natural-k" operands: k-step ks contracts k = 16ks .. 16ks+15 with the instruction's own slot order (a0/a1: k =
+// 2j, 2j+1; a2/a3: k = 8+2j, 9+2j; likewise b0/b1), accumulated over ks = 0..7 in ONE accumulator.  That is the
+// order a library GEMM accumulates in: cuBLAS's nvjet (tcgen05) kernel for X = K.PHI gives the same bits as this
+// chain in all 1.57 M entries of a 32768 x 48 product, the permuted-k chain above differs in ~50 per million
+// (tools/ubench/sketch_order.cu, sketch_umma.cu; profiles/r02c_sketch_bits.txt).  Used where the result is rounded
+// to 16 bit and the reference's bits matter (the Compactor sketch).  Rows: 16-bit, k contiguous, 128 long.
+// w[2*ks] = k-slots (2j, 2j+1), w[2*ks+1] = k-slots (8+2j, 9+2j).
+struct FragNat128 {
+  uint32_t w[16];
+  __device__ __forceinline__ void load(const uint16_t* row, int j) {
+    const uint32_t* r32 = reinterpret_cast<const uint32_t*>(row);
+#pragma unroll
+    for (int i = 0; i < 16; ++i) w[i] = row ? r32[8 * (i >> 1) + 4 * (i & 1) + j] : 0u;
+  }
+};
+
 }  // namespace cvllm

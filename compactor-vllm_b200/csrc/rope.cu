@@ -43,10 +43,10 @@ struct RopeParams {
 };
 
 struct RopeSmem {
-  uint16_t phiT[kRopeSk][128 + 32];                    // PHI^T, 64 B row pad: conflict-free LDS.128
+  uint16_t phiT[kRopeSk][128 + 8];                     // PHI^T, 68-word rows: conflict-free LDS.32 fragments
   // normed pre-RoPE key rows of the tile, double-buffered: one __syncthreads per tile (the barrier of tile i+1
   // orders the sketch reads of tile i before the writes of tile i+2 into the same buffer)
-  uint16_t kpre[2][kRopeMaxHkv][kRopeTok][128 + 32];
+  uint16_t kpre[2][kRopeMaxHkv][kRopeTok][128 + 8];
 };
 
 template <bool BF16>
@@ -223,26 +223,18 @@ __global__ void __launch_bounds__(kRopeThreads, 2) rope_qk_kernel(const RopePara
       const int warp = tid >> 5, lane = tid & 31, r = lane >> 2, j = lane & 3;
       for (int h = warp; h < p.HKV; h += kRopeThreads / 32) {
         const int t_lo = r, t_hi = r + 8;
-        AFrag128 a;
-        a.load(t_lo < nt ? reinterpret_cast<const char*>(sm.kpre[buf][h][t_lo]) : nullptr,
-               t_hi < nt ? reinterpret_cast<const char*>(sm.kpre[buf][h][t_hi]) : nullptr, j);
+        FragNat128 alo, ahi;  // natural-k chain (mma.cuh): cuBLAS's bits for K.PHI
+        alo.load(t_lo < nt ? sm.kpre[buf][h][t_lo] : nullptr, j);
+        ahi.load(t_hi < nt ? sm.kpre[buf][h][t_hi] : nullptr, j);
         uint16_t* xo = reinterpret_cast<uint16_t*>(p.sketch);
 #pragma unroll
         for (int nn = 0; nn < kRopeSk / 8; ++nn) {
           float acc[4] = {0.f, 0.f, 0.f, 0.f};
-          const uint16_t* prow = sm.phiT[nn * 8 + r];
+          const uint32_t* prow = reinterpret_cast<const uint32_t*>(sm.phiT[nn * 8 + r]);
 #pragma unroll
-          for (int c4 = 0; c4 < 4; ++c4) {
-            const uint4 pb = *reinterpret_cast<const uint4*>(prow + (j + 4 * c4) * 8);
-#pragma unroll
-            for (int half = 0; half < 2; ++half) {
-              const int ks = 2 * c4 + half;
-              uint32_t a0, a1, a2, a3, b0, b1;
-              a.regs(ks, a0, a1, a2, a3);
-              bfrag_regs(pb, ks, b0, b1);
-              mma16816<BF16>(acc, a0, a1, a2, a3, b0, b1);
-            }
-          }
+          for (int ks = 0; ks < 8; ++ks)
+            mma16816<BF16>(acc, alo.w[2 * ks], ahi.w[2 * ks], alo.w[2 * ks + 1], ahi.w[2 * ks + 1],
+                           prow[8 * ks + j], prow[8 * ks + 4 + j]);
           const int cx = nn * 8 + 2 * j;
           if (t_lo < nt)
             *reinterpret_cast<uint32_t*>(xo + ((int64_t)(tok0 + t_lo) * p.HKV + h) * kRopeSk + cx) =

@@ -101,6 +101,7 @@ extern "C" int cvllm_set_test_option(const char* name, double value) {
   else if (!strcmp(name, "prefill_threshold")) o.prefill_threshold = (float)value;
   else if (!strcmp(name, "decode_mode")) o.decode_mode = (int)value;
   else if (!strcmp(name, "decode_slots")) o.decode_slots = (int)value;
+  else if (!strcmp(name, "chunk_scores_v1")) o.chunk_scores_v1 = (int)value;
   else {
     cvllm::set_last_error("unknown test option");
     return CVLLM_E_ARG;

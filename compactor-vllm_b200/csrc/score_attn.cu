@@ -514,6 +514,11 @@ __global__ void __launch_bounds__(kScThreads, 1) snap_scores_kernel(const SnapPa
 
 using namespace cvllm;
 
+int cvllm_launch_chunk_scores_umma(const void* q, const void* k, int64_t q_stride_n, int64_t k_stride_n,
+                                   const int32_t* cu, int B, int N, int HQ, int HKV, int chunk, int max_chunks,
+                                   int n_ci, float scale_log2, float* raw, float* partials, bool bf16,
+                                   cudaStream_t st);
+
 static size_t al256(size_t x) { return (x + 255) & ~(size_t)255; }
 static const int kScSmem = kKeyTile * kKRowBytes;  // 40 KB
 
@@ -550,13 +555,21 @@ extern "C" int cvllm_chunk_attn_scores(const void* q, const void* k, int64_t q_s
   p.scale_log2 = sm_scale * 1.4426950408889634f;
   const int64_t items = (int64_t)B * HKV * grid_chunks;
   CVLLM_CHECK_SUPPORTED(items < (1ll << 31));
-  const int grid = (int)(items < sm_count() ? items : sm_count());
-  static std::atomic<uint64_t> attr_bf{0}, attr_h{0};  // 2 K buffers = 80 KB dynamic smem
-  if (dtype == CVLLM_BF16) CVLLM_CHECK_CUDA(ensure_max_dyn_smem((const void*)chunk_scores_kernel<true>, 2 * kScSmem, attr_bf));
-  else CVLLM_CHECK_CUDA(ensure_max_dyn_smem((const void*)chunk_scores_kernel<false>, 2 * kScSmem, attr_h));
-  if (dtype == CVLLM_BF16) chunk_scores_kernel<true><<<grid, kScThreads, 2 * kScSmem, st>>>(p);
-  else chunk_scores_kernel<false><<<grid, kScThreads, 2 * kScSmem, st>>>(p);
-  CVLLM_CHECK_LAUNCH();
+  if (test_options().chunk_scores_v1.load() == 0) {
+    // product path: tcgen05 tiles fed by TMA (score_chunk_umma.cu)
+    const int rc = cvllm_launch_chunk_scores_umma(q, k, q_stride_n, k_stride_n, cu_seqlens, B, N, HQ, HKV, chunk,
+                                                  max_chunks, grid_chunks, p.scale_log2, out, p.partials,
+                                                  dtype == CVLLM_BF16, st);
+    if (rc != CVLLM_OK) return rc;
+  } else {
+    const int grid = (int)(items < sm_count() ? items : sm_count());
+    static std::atomic<uint64_t> attr_bf{0}, attr_h{0};  // 2 K buffers = 80 KB dynamic smem
+    if (dtype == CVLLM_BF16) CVLLM_CHECK_CUDA(ensure_max_dyn_smem((const void*)chunk_scores_kernel<true>, 2 * kScSmem, attr_bf));
+    else CVLLM_CHECK_CUDA(ensure_max_dyn_smem((const void*)chunk_scores_kernel<false>, 2 * kScSmem, attr_h));
+    if (dtype == CVLLM_BF16) chunk_scores_kernel<true><<<grid, kScThreads, 2 * kScSmem, st>>>(p);
+    else chunk_scores_kernel<false><<<grid, kScThreads, 2 * kScSmem, st>>>(p);
+    CVLLM_CHECK_LAUNCH();
+  }
   ChunkFinalizeParams f;
   f.out = out; f.partials = p.partials; f.cu = cu_seqlens; f.accum = accum; f.accum_dtype = accum_dtype;
   f.accum_stride_n = accum_stride_n; f.blend = blend; f.prot_first = prot_first; f.prot_last = prot_last;

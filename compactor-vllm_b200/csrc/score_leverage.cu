@@ -61,7 +61,7 @@ __device__ __forceinline__ float from16(uint16_t x) {
 }
 
 struct LevSmem {
-  uint16_t phiT[kSk][128 + 32];       // PHI^T: sketch-major, d contiguous (+64 B pad: conflict-free LDS.128)
+  uint16_t phiT[kSk][128 + 8];        // PHI^T: sketch-major, d contiguous (68-word rows: conflict-free LDS.32 fragments)
   uint16_t xt[kSk][kXtStride];        // X^T tile: sketch-major, token contiguous
   float g[kSk][kSk + 1];              // Gram accumulator (gram kernel) / unused (score kernel)
   float sv[kSk][kSk];                 // round16(V |lam|^-1/2) (score kernel) / staging (gram kernel)
@@ -100,24 +100,18 @@ __device__ __forceinline__ void sketch_tile(LevSmem& sm, const LevParams& p, int
     auto krow = [&](int t) -> const char* {
       return t < nt ? kb + ((int64_t)(tok0 + t) * p.k_stride_n + (int64_t)h * p.k_stride_h) * 2 : nullptr;
     };
-    AFrag128 a;
-    a.load(krow(t_lo), krow(t_hi), j);
+    // natural-k chain (mma.cuh): the bits of the reference's cuBLAS GEMM at compactor.py:158
+    FragNat128 alo, ahi;
+    alo.load(reinterpret_cast<const uint16_t*>(krow(t_lo)), j);
+    ahi.load(reinterpret_cast<const uint16_t*>(krow(t_hi)), j);
 #pragma unroll
     for (int nn = 0; nn < kSk / 8; ++nn) {
       float acc[4] = {0.f, 0.f, 0.f, 0.f};
-      const uint16_t* prow = sm.phiT[nn * 8 + r];
+      const uint32_t* prow = reinterpret_cast<const uint32_t*>(sm.phiT[nn * 8 + r]);
 #pragma unroll
-      for (int cc = 0; cc < 4; ++cc) {
-        const uint4 pb = *reinterpret_cast<const uint4*>(prow + (j + 4 * cc) * 8);
-#pragma unroll
-        for (int half = 0; half < 2; ++half) {
-          const int ks = 2 * cc + half;
-          uint32_t a0, a1, a2, a3, b0, b1;
-          a.regs(ks, a0, a1, a2, a3);
-          bfrag_regs(pb, ks, b0, b1);
-          mma16816<BF16>(acc, a0, a1, a2, a3, b0, b1);
-        }
-      }
+      for (int ks = 0; ks < 8; ++ks)
+        mma16816<BF16>(acc, alo.w[2 * ks], ahi.w[2 * ks], alo.w[2 * ks + 1], ahi.w[2 * ks + 1], prow[8 * ks + j],
+                       prow[8 * ks + 4 + j]);
       // acc: rows t_lo / t_hi, sketch cols nn*8 + 2j, +1
       const int c0 = nn * 8 + 2 * j;
 #pragma unroll

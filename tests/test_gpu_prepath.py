@@ -160,6 +160,30 @@ def test_leverage_from_fused_sketch_is_bit_identical(lens):
     assert torch.equal(a[~nan], b[~nan])
 
 
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_sketch_bits_equal_the_reference_gemm(dtype):
+    """The Compactor sketch X = K.PHI is rounded to 16 bit and feeds an ill-conditioned factorisation
+    (DESIGN 3.4), so its BITS matter: the kernel accumulates in the natural k order of a library GEMM
+    (mma.cuh FragNat128) and must reproduce the reference's own call — torch.matmul on the transposed
+    view, compression/compactor.py:158 — at the headline shape.  Tolerates a handful of flipped ulps in case
+    another cuBLAS build picks a split-K kernel (measured here: 0 of 12.6 M)."""
+    from compactor_vllm.layers.rotary_embedding import RotaryEmbedding
+
+    N, HQ, HKV, D = 32768, 8, 8, 128
+    g = torch.Generator(device=DEV).manual_seed(3)
+    basis = torch.randn((HKV, 12, D), generator=g, device=DEV)
+    coef = torch.randn((N, HKV, 12), generator=g, device=DEV) * torch.linspace(2.0, 0.2, 12, device=DEV)
+    k = (torch.einsum("nhr,hrd->nhd", coef, basis) + 0.3 * torch.randn((N, HKV, D), generator=g, device=DEV))
+    k = k.to(dtype).contiguous()
+    q = torch.randn((N, HQ, D), generator=g, device=DEV).to(dtype)
+    phi = (torch.randn((D, 48), generator=g, device=DEV) / 48 ** 0.5).to(dtype)
+    rope = RotaryEmbedding(D, D, 8, 500000.0, None).to(DEV)
+    _, _, sk = rope.forward_fused(torch.zeros(N, dtype=torch.int64, device=DEV), q, k, PHI=phi)
+    ref = torch.matmul(k.transpose(0, 1), phi).transpose(0, 1)  # [N, HKV, 48]
+    differ = int((_bits(sk) != _bits(ref)).sum())
+    assert differ <= 1e-5 * ref.numel(), f"{differ} of {ref.numel()} sketch entries differ from cuBLAS"
+
+
 @pytest.mark.parametrize("name", ["rmsnorm_bf16_128", "rmsnorm_bf16_4096", "rmsnorm_f16_1024"])
 def test_rmsnorm_golden(name):
     from compactor_vllm.layers.layernorm import RMSNorm
