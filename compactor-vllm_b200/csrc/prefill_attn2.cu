@@ -312,6 +312,28 @@ prefill_attn2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
 
       // ---- P = exp2(S*scale - m_ref), row sum, 16-bit pack, back to TMEM over S ----
       const float neg_m = (m_ref == -INFINITY) ? 0.f : -m_ref;
+#ifdef CVLLM_PREFILL_F32X2
+      // packed fp32 pairs: one FFMA2 scales and shifts two logits, one FADD2 adds two probabilities to the row sum
+      // (half the FMA-pipe issue slots of the scalar form; same roundings)
+      const float2 sc2 = make_float2(p.scale_log2, p.scale_log2), nm2 = make_float2(neg_m, neg_m);
+      float2 l2a = make_float2(0.f, 0.f), l2b = make_float2(0.f, 0.f);
+#pragma unroll
+      for (int c = 0; c < kBN / 32; ++c) {
+        uint32_t pk[16];
+#pragma unroll
+        for (int i = 0; i < 16; i += 2) {
+          const float2 t0 = __ffma2_rn(make_float2(s[c * 32 + 2 * i], s[c * 32 + 2 * i + 1]), sc2, nm2);
+          const float2 t1 = __ffma2_rn(make_float2(s[c * 32 + 2 * i + 2], s[c * 32 + 2 * i + 3]), sc2, nm2);
+          const float2 e0 = make_float2(ex2(t0.x), ex2(t0.y)), e1 = make_float2(ex2(t1.x), ex2(t1.y));
+          l2a = __fadd2_rn(l2a, e0);
+          l2b = __fadd2_rn(l2b, e1);
+          pk[i] = pack2<BF16>(e0.x, e0.y);
+          pk[i + 1] = pack2<BF16>(e1.x, e1.y);
+        }
+        tmem_st16(s_tmem + c * 16, pk);
+      }
+      l += (l2a.x + l2b.x) + (l2a.y + l2b.y);
+#else
       float l0 = 0.f, l1 = 0.f;
 #pragma unroll
       for (int c = 0; c < kBN / 32; ++c) {
@@ -327,6 +349,7 @@ prefill_attn2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
         tmem_st16(s_tmem + c * 16, pk);
       }
       l += l0 + l1;
+#endif
       tc_wait_st();
       tc_fence_before();
       mbar_arrive(&sm.p_full[t]);

@@ -184,61 +184,71 @@ chunk_scores_umma_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
         const uint32_t s_t = tmem + buf * kTile + lane_base;
         mbar_wait(&sm.s_full[buf], (k >> 1) & 1);
         tc_fence_after();
-        // pass 1: row max over the chunk's keys (32 columns at a time: the 128 accumulators own the registers)
+        // Three passes over the TMEM tile in 16-column pieces, software-pipelined: the load of piece c+1 is in
+        // flight while piece c is processed (tcgen05.wait::ld waits for every outstanding load, so it sits
+        // AFTER the work on the current piece).  pass 1: row max | pass 2: e = exp2(s*scale - m), row sum,
+        // e written back over S | pass 3: acc += e / l.
+        uint32_t pa[16], pb[16];
         float mx = -INFINITY;
+        tmem_ld16(s_t, pa);
+        tc_wait_ld();
 #pragma unroll
-        for (int c = 0; c < kTile / 32; ++c) {
-          uint32_t t0[32];
-          tmem_ld32(s_t + c * 32, t0);
-          tc_wait_ld();
+        for (int c = 0; c < kTile / 16; ++c) {
+          uint32_t(&cur)[16] = (c & 1) ? pb : pa;
+          uint32_t(&nxt)[16] = (c & 1) ? pa : pb;
+          if (c + 1 < kTile / 16) tmem_ld16(s_t + (c + 1) * 16, nxt);
+          else tmem_ld16(s_t, nxt);  // first piece of pass 2
           float m0 = -INFINITY, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
 #pragma unroll
-          for (int i = 0; i < 32; i += 4) {
-            float a0 = __uint_as_float(t0[i]), a1 = __uint_as_float(t0[i + 1]);
-            float a2 = __uint_as_float(t0[i + 2]), a3 = __uint_as_float(t0[i + 3]);
+          for (int i = 0; i < 16; i += 4) {
+            float a0 = __uint_as_float(cur[i]), a1 = __uint_as_float(cur[i + 1]);
+            float a2 = __uint_as_float(cur[i + 2]), a3 = __uint_as_float(cur[i + 3]);
             if (ragged) {
-              if (c * 32 + i >= M) a0 = -INFINITY;
-              if (c * 32 + i + 1 >= M) a1 = -INFINITY;
-              if (c * 32 + i + 2 >= M) a2 = -INFINITY;
-              if (c * 32 + i + 3 >= M) a3 = -INFINITY;
+              if (c * 16 + i >= M) a0 = -INFINITY;
+              if (c * 16 + i + 1 >= M) a1 = -INFINITY;
+              if (c * 16 + i + 2 >= M) a2 = -INFINITY;
+              if (c * 16 + i + 3 >= M) a3 = -INFINITY;
             }
             m0 = fmaxf(m0, a0); m1 = fmaxf(m1, a1); m2 = fmaxf(m2, a2); m3 = fmaxf(m3, a3);
           }
           mx = fmaxf(mx, fmaxf(fmaxf(m0, m1), fmaxf(m2, m3)));
+          tc_wait_ld();
         }
         const float neg_m = -mx * p.scale_log2;  // M >= 1: every row has at least one live key
-        // pass 2: e = exp2(s * scale - m), row sum; e goes back over S
         float l0 = 0.f, l1 = 0.f;
 #pragma unroll
-        for (int c = 0; c < kTile / 32; ++c) {
-          uint32_t t0[32];
-          tmem_ld32(s_t + c * 32, t0);
-          tc_wait_ld();
+        for (int c = 0; c < kTile / 16; ++c) {  // kTile / 16 is even: pass 2 starts on pa again
+          uint32_t(&cur)[16] = (c & 1) ? pb : pa;
+          uint32_t(&nxt)[16] = (c & 1) ? pa : pb;
+          if (c + 1 < kTile / 16) tmem_ld16(s_t + (c + 1) * 16, nxt);
 #pragma unroll
-          for (int i = 0; i < 32; i += 2) {
-            float e0 = ex2(fmaf(__uint_as_float(t0[i]), p.scale_log2, neg_m));
-            float e1 = ex2(fmaf(__uint_as_float(t0[i + 1]), p.scale_log2, neg_m));
+          for (int i = 0; i < 16; i += 2) {
+            float e0 = ex2(fmaf(__uint_as_float(cur[i]), p.scale_log2, neg_m));
+            float e1 = ex2(fmaf(__uint_as_float(cur[i + 1]), p.scale_log2, neg_m));
             if (ragged) {
-              if (c * 32 + i >= M) e0 = 0.f;
-              if (c * 32 + i + 1 >= M) e1 = 0.f;
+              if (c * 16 + i >= M) e0 = 0.f;
+              if (c * 16 + i + 1 >= M) e1 = 0.f;
             }
             l0 += e0;
             l1 += e1;
-            t0[i] = __float_as_uint(e0);
-            t0[i + 1] = __float_as_uint(e1);
+            cur[i] = __float_as_uint(e0);
+            cur[i + 1] = __float_as_uint(e1);
           }
-          tmem_st32(s_t + c * 32, t0);
+          tmem_st16(s_t + c * 16, cur);
+          tc_wait_ld();
         }
         tc_wait_st();
-        // pass 3: acc += e / l (rows beyond the chunk contribute nothing)
-        const float inv = (row < M) ? 1.f / (l0 + l1) : 0.f;
+        const float inv = (row < M) ? 1.f / (l0 + l1) : 0.f;  // rows beyond the chunk contribute nothing
+        tmem_ld16(s_t, pa);
+        tc_wait_ld();
 #pragma unroll
-        for (int c = 0; c < kTile / 32; ++c) {
-          uint32_t t0[32];
-          tmem_ld32(s_t + c * 32, t0);
+        for (int c = 0; c < kTile / 16; ++c) {
+          uint32_t(&cur)[16] = (c & 1) ? pb : pa;
+          uint32_t(&nxt)[16] = (c & 1) ? pa : pb;
+          if (c + 1 < kTile / 16) tmem_ld16(s_t + (c + 1) * 16, nxt);
+#pragma unroll
+          for (int i = 0; i < 16; ++i) acc[c * 16 + i] = fmaf(__uint_as_float(cur[i]), inv, acc[c * 16 + i]);
           tc_wait_ld();
-#pragma unroll
-          for (int i = 0; i < 32; ++i) acc[c * 32 + i] = fmaf(__uint_as_float(t0[i]), inv, acc[c * 32 + i]);
         }
         tc_fence_before();
         mbar_arrive(&sm.s_empty[buf]);

@@ -457,7 +457,7 @@ __global__ void __launch_bounds__(kTileTok) sel_gather_kernel(
       s_dst[tid * H + h] = dst;
     }
   }
-  if (tile == 0 && tid < H && s_act[tid])
+  if (tile == 0 && blockIdx.z == 0 && tid < H && s_act[tid])
     bh_lens[b * H + tid] = w.len0[b * H + tid] + (int)(s_gt_all[tid] + min(s_tie_all[tid], s_ties[tid]));
   __syncthreads();
   // cooperative row copy: VEC_PER_ROW lanes per (token, head) row
@@ -465,7 +465,10 @@ __global__ void __launch_bounds__(kTileTok) sel_gather_kernel(
   const int vec = tid % VEC_PER_ROW, rin = tid / VEC_PER_ROW;
   const int n_rows = min(kTileTok, len - tile * kTileTok) * H;
   const int64_t tok0 = beg + tile * kTileTok;
-  for (int r0 = 0; r0 < n_rows; r0 += 4 * ROWS_PER_IT) {
+  // gridDim.z CTAs share a tile's rows (each recomputes the destinations above, ~1 us, and copies every z-th
+  // group): the copy is 134 MB of pure bandwidth at 32K and one 256-thread CTA per 256 tokens (128 CTAs, 32 KB in
+  // flight each) reached 2.4 TB/s
+  for (int r0 = blockIdx.z * 4 * ROWS_PER_IT; r0 < n_rows; r0 += gridDim.z * 4 * ROWS_PER_IT) {
     uint4 kk[4], vv[4];
     int64_t d[4];
 #pragma unroll
@@ -582,8 +585,11 @@ extern "C" int cvllm_select_store_topk(const float* scores, int64_t s_stride_n, 
     sel_pass_kernel<true><<<grid, kPassThreads, 0, st>>>(scores, s_stride_n, cu_seqlens_k, HKV, pass, w);
   sel_count_heads_kernel<<<grid, kPassThreads, 0, st>>>(scores, s_stride_n, cu_seqlens_k, HKV, w);
   CVLLM_CHECK_LAUNCHES(12);
+  // enough copy CTAs to fill the chip a few times over: 4 per tile at long prompts, 1 when the grid is already wide
+  const int64_t gtiles = (int64_t)grid.x * grid.y;
+  const dim3 ggrid(grid.x, grid.y, gtiles >= 4 * sm_count() ? 1 : 4);
 #define G(V)                                                                                            \
-  launch_sel_gather<V>(grid, st, scores, s_stride_n, keys, vals, sk_n / per16, sk_h / per16, sv_n / per16, \
+  launch_sel_gather<V>(ggrid, st, scores, s_stride_n, keys, vals, sk_n / per16, sk_h / per16, sv_n / per16, \
                        sv_h / per16, cu_seqlens_k, batch_mapping, page_table, bh_lens, k_cache, v_cache,   \
                        HKV, PS, NLP, w)
   switch (vpr) {
