@@ -279,20 +279,25 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_const
 
       // ---- P = exp2(S*scale - m_ref), row sum, bf16 pack, back to TMEM ----
       const float neg_m = (m_ref == -INFINITY) ? 0.f : -m_ref;
-      float lsum = 0.f;
+      // packed fp32 pairs (FFMA2 / FADD2: half the FMA-pipe issue slots of the scalar form, same roundings)
+      const float2 sc2 = make_float2(p.scale_log2, p.scale_log2), nm2 = make_float2(neg_m, neg_m);
+      float2 l2a = make_float2(0.f, 0.f), l2b = make_float2(0.f, 0.f);
 #pragma unroll
       for (int c = 0; c < kBN / 64; ++c) {
         uint32_t pk[32];
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          const float p0 = ex2(fmaf(s[c * 64 + 2 * i], p.scale_log2, neg_m));
-          const float p1 = ex2(fmaf(s[c * 64 + 2 * i + 1], p.scale_log2, neg_m));
-          lsum += p0 + p1;
-          pk[i] = pack2<BF16>(p0, p1);
+        for (int i = 0; i < 32; i += 2) {
+          const float2 t0 = __ffma2_rn(make_float2(s[c * 64 + 2 * i], s[c * 64 + 2 * i + 1]), sc2, nm2);
+          const float2 t1 = __ffma2_rn(make_float2(s[c * 64 + 2 * i + 2], s[c * 64 + 2 * i + 3]), sc2, nm2);
+          const float2 e0 = make_float2(ex2(t0.x), ex2(t0.y)), e1 = make_float2(ex2(t1.x), ex2(t1.y));
+          l2a = __fadd2_rn(l2a, e0);
+          l2b = __fadd2_rn(l2b, e1);
+          pk[i] = pack2<BF16>(e0.x, e0.y);
+          pk[i + 1] = pack2<BF16>(e1.x, e1.y);
         }
         tmem_st32(s_tmem + c * 32, pk);
       }
-      l += lsum;
+      l += (l2a.x + l2b.x) + (l2a.y + l2b.y);
       tc_wait_st();
       tc_fence_before();
       mbar_arrive(&sm.p_full[sb]);

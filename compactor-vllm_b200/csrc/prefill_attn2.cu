@@ -312,7 +312,7 @@ prefill_attn2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
 
       // ---- P = exp2(S*scale - m_ref), row sum, 16-bit pack, back to TMEM over S ----
       const float neg_m = (m_ref == -INFINITY) ? 0.f : -m_ref;
-#ifdef CVLLM_PREFILL_F32X2
+#ifndef CVLLM_PREFILL_SCALAR_SOFTMAX  // A/B on B200 (r02d): packed 7.62-7.68 ms vs scalar 7.95-8.05 ms at 32K
       // packed fp32 pairs: one FFMA2 scales and shifts two logits, one FADD2 adds two probabilities to the row sum
       // (half the FMA-pipe issue slots of the scalar form; same roundings)
       const float2 sc2 = make_float2(p.scale_log2, p.scale_log2), nm2 = make_float2(neg_m, neg_m);

@@ -288,6 +288,53 @@ def test_leverage_low_rank_keys_statistics(dtype, lens, H, chunk):
         assert _overlap(norm, exact_n) >= _overlap(ref_n, exact_n) - 0.03
 
 
+def _reference_arithmetic_on_device(keys, lens, phi, chunk, reg=5e-3):
+    """compression/compactor.py:153-210 re-issued with torch on the SAME device — the reference's own call
+    sequence (cuBLAS GEMM on the transposed view, in-place mean subtraction, batched Gram GEMM, 16-bit roundings
+    where torch puts them) — with the `gesvda` SVD replaced by the factorisation it approximates: fp64 `eigh`
+    of the fp32 Gram, S = |lambda|.  On the B200 the unmodified reference is itself only 99.25 % within 2e-2 of
+    this on low-rank keys (profiles/r02c_leverage_selfdistance.json: ref_eigh64_vs_ref) while this repo is at
+    100.00 % (ours_vs_eigh64), so this is the tighter pin."""
+    X = torch.matmul(keys.transpose(0, 1), phi)  # [H, N, k]
+    H, N, k = X.shape
+    coalesced, _ = osc.split_into_chunks(lens, chunk)
+    pieces = torch.split(X, coalesced, dim=-2)
+    out = []
+    for L, piece in zip(coalesced, pieces):
+        c = piece.view(H, -1, chunk, k) if (chunk > 0 and L % chunk == 0) else piece.unsqueeze(1)
+        c = c.clone()
+        c.sub_(c.mean(dim=-2, keepdim=True))
+        G = torch.matmul(c.transpose(-1, -2), c).to(torch.float32)
+        G.diagonal(dim1=-2, dim2=-1).add_(reg)
+        lam, V = torch.linalg.eigh(G.double())
+        SV = (V * lam.abs().rsqrt().unsqueeze(-2)).to(torch.float32).to(X.dtype)
+        U = torch.matmul(c, SV)
+        out.append((U * U).sum(dim=-1).clamp_min_(0.0).view(H, -1).transpose(-1, -2))
+    return torch.cat(out, dim=0)
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("lens,chunk", [([4096], 512), ([1536, 700, 49], 512), ([32768], 512)])
+def test_leverage_matches_reference_arithmetic_on_device(dtype, lens, chunk):
+    """Low-rank keys, where one flipped ulp of the 16-bit sketch moves a chunk's scores by O(1): the kernel
+    chain has to reproduce the reference's cuBLAS bits through the Gram (natural-k sketch chain, sequential
+    Gram accumulation) and factorise exactly (fp64 tridiagonal QL).  Bar: >= 99.95 % of the scores within
+    2e-2 * max(1, |s|), none beyond 0.1, top-half overlap >= 99.9 %."""
+    N, H, D = sum(lens), 8, 128
+    scale = 1.0 if dtype == torch.bfloat16 else 0.1  # fp16: keep the Gram below 65504
+    keys = (_structured_keys(N, H, D, torch.float32, seed=N) * scale).to(dtype).to(DEV)
+    phi = make_phi(D, 48, dtype, DEV)
+    got = approximate_leverage_scores(keys, lens, phi, normalize=False, chunk_size=chunk).float()
+    ref = _reference_arithmetic_on_device(keys, lens, phi, chunk).float()
+    _, chunk_lens = osc.split_into_chunks(lens, chunk)
+    full = torch.cat([torch.full((L,), L >= 48, dtype=torch.bool) for L in chunk_lens]).to(DEV)
+    err = (got - ref).abs() / ref.abs().clamp_min(1.0)
+    assert torch.isfinite(got).all()
+    assert (err[full] <= 2e-2).float().mean().item() >= 0.9995, (err[full] <= 2e-2).float().mean().item()
+    assert err[full].max().item() <= 0.1, err[full].max().item()
+    assert _overlap(got[full], ref[full]) >= 0.999
+
+
 def test_leverage_one_token_chunk_is_nan():
     """a 1-token tail chunk z-scores to 0/0 = NaN, which the ranking keeps first."""
     lens, H = [513], 8
@@ -295,6 +342,41 @@ def test_leverage_one_token_chunk_is_nan():
     phi = make_phi(128, 48, torch.bfloat16, "cpu")
     out = approximate_leverage_scores(keys.to(DEV), lens, phi.to(DEV), normalize=True, chunk_size=512)
     assert torch.isnan(out[512]).all() and torch.isfinite(out[:512]).all()
+
+
+def test_plugin_split_scoring_equals_single_call():
+    """CompactorCompression.post_rope_scoring runs the q/k half of the chunk scorer on a second side stream
+    beside the leverage chain and the epilogue behind it (cvllm_chunk_attn_scores_raw / _finalize): same bits as
+    the single-stream call, with and without a store stream, twice in a row (workspace reuse)."""
+    from compactor_vllm.compression.compactor import CompactorCompression
+    from compactor_vllm.compression.compression_config import CompressionMethod
+    from compactor_vllm.utils.arguments import max_tokens_to_retain, tokens_to_retain
+    from compactor_vllm.utils.context import CompressionContext, Context
+
+    lens, HQ, HKV, D, dtype = [1500, 77, 600], 32, 8, 128, torch.bfloat16
+    N = sum(lens)
+    keys_pre = _structured_keys(N, HKV, D, dtype, seed=21).to(DEV)
+    q, k, v = fused_qkv(N, HQ, HKV, D, dtype, DEV, seed=22)
+    cu = _cu(lens).to(DEV)
+    pf, pl = [16] * 3, [64] * 3
+    cc = CompressionContext(CompressionMethod.COMPACTOR, 512,
+                            torch.tensor(tokens_to_retain(lens, [0.5] * 3, pf, pl, HKV), dtype=torch.int32, device=DEV),
+                            max_tokens_to_retain(lens, HKV), lens, make_phi(D, 48, dtype, DEV), pf, pl)
+    results = []
+    for store in (None, torch.cuda.Stream(priority=-1), torch.cuda.Stream()):
+        ctx = Context(is_prefill=True, do_compression=True, cu_seqlens_q=cu, cu_seqlens_k=cu, max_seqlen_q=max(lens),
+                      max_seqlen_k=max(lens), compression_context=cc, STORE_STREAM=store)
+        for _ in range(2):
+            pre = CompactorCompression.pre_rope_scoring(q, keys_pre, v, ctx)
+            out = CompactorCompression.post_rope_scoring(q, k, v, pre, ctx)
+            if store is not None:
+                torch.cuda.current_stream().wait_stream(store)
+            torch.cuda.synchronize()
+            results.append(out.clone())
+    for r in results[1:]:
+        assert torch.equal(torch.isinf(r), torch.isinf(results[0]))
+        fin = torch.isfinite(results[0])
+        assert torch.equal(r[fin], results[0][fin])
 
 
 # ---------------------------------------------------------------- end-to-end Compactor scores
