@@ -393,7 +393,7 @@ def bind_to_gpu_numa(local: int) -> dict:
     return info
 
 
-def copy_roofline(h_in, d_in, d_out, h_out, ranks, reps: int = 3) -> dict:
+def copy_roofline(h_in, d_in, d_out, h_out, ranks, reps: int = 3, kernel_fn=None) -> dict:
     """The box's own copy ceiling on the e2e leg's buffers: H2D alone, D2H alone, both at once (two streams),
     every rank copying at the same time; GB/s summed over ranks and the duplex time of one step's bytes."""
     s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
@@ -422,7 +422,30 @@ def copy_roofline(h_in, d_in, d_out, h_out, ranks, reps: int = 3) -> dict:
     by_out = h_out.numel() * h_out.element_size()
     run(True, True)
     t_in, t_out, t_dup = run(True, False), run(False, True), run(True, True)
-    return {"h2d_gbs_alone": ranks.sum(by_in / t_in / 1e6), "d2h_gbs_alone": ranks.sum(by_out / t_out / 1e6),
+    overlap = {}
+    if kernel_fn is not None:
+        # does a DMA copy overlap a running kernel on this box?  (seen both ways on this pool's single-GPU boxes:
+        # some run the double-buffered loop at the copy bound, some serialise H2D behind the step's kernels)
+        def both(do_copy: bool, do_kernel: bool) -> float:
+            ranks.barrier()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            s1.wait_event(a)
+            if do_kernel:
+                kernel_fn()
+            if do_copy:
+                with torch.cuda.stream(s1):
+                    for h, d in zip(h_in, d_in):
+                        d.copy_(h, non_blocking=True)
+            torch.cuda.current_stream().wait_stream(s1)
+            b.record()
+            b.synchronize()
+            return a.elapsed_time(b)
+        both(True, True)
+        t_k, t_c, t_b = both(False, True), both(True, False), both(True, True)
+        overlap = {"kernels_ms": t_k, "h2d_ms": t_c, "kernels_and_h2d_ms": t_b,
+                   "h2d_overlaps_kernels_frac": ranks.max(-(t_k + t_c - t_b) / min(t_k, t_c)) * -1.0}
+    return {**overlap, "h2d_gbs_alone": ranks.sum(by_in / t_in / 1e6), "d2h_gbs_alone": ranks.sum(by_out / t_out / 1e6),
             "duplex_gbs": ranks.sum((by_in + by_out) / t_dup / 1e6), "duplex_ms_per_step": ranks.max(t_dup),
             "note": "GB/s summed over ranks, all ranks copying at once; duplex = one step's H2D and D2H together"}
 
@@ -970,7 +993,8 @@ def main():
         barrier()
         pipe_ms = max_over_ranks((time.perf_counter() - t0) * 1e3 / (2 * n_e2e))
         try:
-            roofc = copy_roofline([h_kpre, h_qkv], [d_kpre, d_qkv], w.prefill_step(compress=False), h_out, ranks)
+            roofc = copy_roofline([h_kpre, h_qkv], [d_kpre, d_qkv], w.prefill_step(compress=False), h_out, ranks,
+                                  kernel_fn=lambda: w.prefill_step())
         except Exception as ex:
             roofc = {"error": repr(ex)[:160]}
         e2e = {"value": flops * world / (pipe_ms * 1e-3) / 1e12, "unit": "TFLOP/s",

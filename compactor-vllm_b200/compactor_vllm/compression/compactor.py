@@ -292,7 +292,8 @@ def _chunk_scores_raw(q, k, cu_seqlens_qk, max_seqlen_qk, chunk_size, sm_scale):
                      device=dev)
     rc = L.cvllm_chunk_attn_scores_raw(
         N.ptr(q), N.ptr(k), q.stride(0), k.stride(0), N.ptr(cu), B, Ntok, HQ, HKV, D, int(chunk_size),
-        int(max_seqlen_qk), float(sm_scale), N.ptr(out), N.dtype_code(q.dtype), N.ptr(ws), ws.numel(), N.stream(dev))
+        int(max_seqlen_qk), float(sm_scale), N.ptr(out), N.dtype_code(q.dtype), 1, N.ptr(ws), ws.numel(),
+        N.stream(dev))
     N.check(rc, "cvllm_chunk_attn_scores_raw")
     return out, ws, cu, B, HKV
 

@@ -517,7 +517,7 @@ using namespace cvllm;
 int cvllm_launch_chunk_scores_umma(const void* q, const void* k, int64_t q_stride_n, int64_t k_stride_n,
                                    const int32_t* cu, int B, int N, int HQ, int HKV, int chunk, int max_chunks,
                                    int n_ci, float scale_log2, float* raw, float* partials, bool bf16,
-                                   cudaStream_t st);
+                                   bool slim, cudaStream_t st);
 
 static size_t al256(size_t x) { return (x + 255) & ~(size_t)255; }
 static const int kScSmem = kKeyTile * kKRowBytes;  // 40 KB
@@ -528,7 +528,8 @@ extern "C" size_t cvllm_chunk_attn_scores_workspace_bytes(int B, int N, int HKV,
   return al256((size_t)B * max_chunks * HKV * 2 * sizeof(float));
 }
 
-// phases: 1 = column sums + per-item partials (reads q, k), 2 = z-score / blend / protection (reads accum), 3 = both
+// phases: 1 = column sums + per-item partials (reads q, k), 2 = z-score / blend / protection (reads accum), 3 = both;
+// | 4 = phase 1 with the small shared-memory footprint (runs beside other kernels' CTAs)
 static int chunk_scores_impl(const void* q, const void* k, int64_t q_stride_n, int64_t k_stride_n,
                              const int32_t* cu_seqlens, int B, int N, int HQ, int HKV, int D,
                              int chunk, int max_seqlen, float sm_scale, int normalize,
@@ -562,7 +563,7 @@ static int chunk_scores_impl(const void* q, const void* k, int64_t q_stride_n, i
     // product path: tcgen05 tiles fed by TMA (score_chunk_umma.cu)
     const int rc = cvllm_launch_chunk_scores_umma(q, k, q_stride_n, k_stride_n, cu_seqlens, B, N, HQ, HKV, chunk,
                                                   max_chunks, grid_chunks, p.scale_log2, out, p.partials,
-                                                  dtype == CVLLM_BF16, st);
+                                                  dtype == CVLLM_BF16, (phases & 4) != 0, st);
     if (rc != CVLLM_OK) return rc;
   } else {
     const int grid = (int)(items < sm_count() ? items : sm_count());
@@ -602,10 +603,11 @@ extern "C" int cvllm_chunk_attn_scores(const void* q, const void* k, int64_t q_s
 extern "C" int cvllm_chunk_attn_scores_raw(const void* q, const void* k, int64_t q_stride_n, int64_t k_stride_n,
                                            const int32_t* cu_seqlens, int B, int N, int HQ, int HKV, int D,
                                            int chunk, int max_seqlen, float sm_scale, float* out, int dtype,
-                                           void* workspace, size_t workspace_bytes, cvllm_stream_t stream) {
+                                           int cotenant, void* workspace, size_t workspace_bytes,
+                                           cvllm_stream_t stream) {
   return chunk_scores_impl(q, k, q_stride_n, k_stride_n, cu_seqlens, B, N, HQ, HKV, D, chunk, max_seqlen, sm_scale,
                            0, nullptr, 2, 0, 1.0f, nullptr, nullptr, out, dtype, workspace, workspace_bytes, stream,
-                           1);
+                           cotenant ? 5 : 1);
 }
 
 extern "C" int cvllm_chunk_attn_scores_finalize(const int32_t* cu_seqlens, int B, int N, int HKV, int chunk,
