@@ -236,8 +236,8 @@ class Workload:
 
     def compress_only(self):
         """score -> select -> store chain alone (KV-compress Mtok/s): the same plugin calls and side streams as the
-        step (leverage chain on the store stream, the q/k half of the chunk scorer beside it on the plugin's second
-        side stream, selection + compaction behind both), no attention kernel.  Capturable in a CUDA graph."""
+        step (scoring, selection and compaction on the store stream), no attention kernel.  Capturable in a CUDA
+        graph."""
         from compactor_vllm.compression.common import extract_and_store_top_kv
         from compactor_vllm.utils.context import get_context
         from compactor_vllm.utils.helpers import maybe_execute_in_stream

@@ -69,10 +69,6 @@ _SIGNATURES = {
     "cvllm_chunk_attn_scores_workspace_bytes": (_sz, [_i, _i, _i, _i]),
     "cvllm_chunk_attn_scores": (_i, [_p, _p, _i64, _i64, _p, _i, _i, _i, _i, _i, _i, _i, _f, _i,
                                      _p, _i, _i64, _f, _p, _p, _p, _i, _p, _sz, _p]),
-    "cvllm_chunk_attn_scores_raw": (_i, [_p, _p, _i64, _i64, _p, _i, _i, _i, _i, _i, _i, _i, _f, _p, _i, _i, _p,
-                                         _sz, _p]),
-    "cvllm_chunk_attn_scores_finalize": (_i, [_p, _i, _i, _i, _i, _i, _i, _p, _i, _i64, _f, _p, _p, _p, _p, _sz,
-                                              _p]),
     "cvllm_snapkv_scores_workspace_bytes": (_sz, [_i, _i, _i, _i, _i]),
     "cvllm_snapkv_scores": (_i, [_p, _p, _i64, _i64, _p, _p, _i, _i, _i, _i, _i, _i, _i, _f, _i,
                                  _i, _p, _i, _p, _sz, _p]),

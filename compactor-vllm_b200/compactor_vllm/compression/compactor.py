@@ -50,29 +50,15 @@ class CompactorCompression(BaseCompressionMethod):
         # the stream itself, its only consumer (extract_and_store_top_kv in Attention.forward)
         # runs on the same stream, and the attention kernel on the main stream starts without
         # waiting for any of it — scoring, selection and compaction all overlap attention.
-        kwargs = dict(
+        return maybe_execute_in_stream(
+            non_causal_attn_scores,
+            q, k, v, context.cu_seqlens_q, context.max_seqlen_q,
             chunk_size=CompactorCompression.chunk_size, sm_scale=1.0, normalize=True,
             accum_scores=pre_rope_scores, context_lens=cc.context_lens,
             protected_first_tokens=cc.protected_first_tokens,
             protected_last_tokens=cc.protected_last_tokens, accum_blending=0.5,
+            STORE_STREAM=context.STORE_STREAM,
         )
-        store = context.STORE_STREAM
-        if store is None or pre_rope_scores is None or q.shape[0] == 0:
-            return maybe_execute_in_stream(non_causal_attn_scores, q, k, v, context.cu_seqlens_q,
-                                           context.max_seqlen_q, STORE_STREAM=store, **kwargs)
-        # The q/k half of the scorer (column sums) does not need the leverage scores, and the leverage chain's
-        # eigensolver is a ~250 us latency chain that leaves the SMs mostly idle: run that half on a second side
-        # stream forked from the caller's stream (q and k are ready there), and only the z-score / blend /
-        # protection epilogue behind the leverage kernels on STORE_STREAM.
-        aux = _aux_stream(q.device, store)
-        aux.wait_stream(torch.cuda.current_stream(q.device))
-        with torch.cuda.stream(aux):
-            state = _chunk_scores_raw(q, k, context.cu_seqlens_q, context.max_seqlen_q,
-                                      CompactorCompression.chunk_size, 1.0)
-        q.record_stream(aux)
-        k.record_stream(aux)
-        return maybe_execute_in_stream(_chunk_scores_finalize, state, aux, context.cu_seqlens_q,
-                                       context.max_seqlen_q, STORE_STREAM=store, **kwargs)
 
 
 def split_into_chunks(xs, chunk_size):
@@ -120,19 +106,6 @@ def _protected_counts(pf: tuple, pl: tuple, dev: torch.device) -> torch.Tensor:
             _OFFSETS_CACHE.clear()
         _OFFSETS_CACHE[key] = t
     return t
-
-
-_AUX_STREAMS: dict = {}
-
-
-def _aux_stream(dev: torch.device, like: torch.cuda.Stream) -> torch.cuda.Stream:
-    """One second side stream per device, at STORE_STREAM's priority (its kernel should get SMs as attention
-    CTAs retire, like the rest of the chain)."""
-    key = (dev.index, like.priority)
-    st = _AUX_STREAMS.get(key)
-    if st is None:
-        st = _AUX_STREAMS[key] = torch.cuda.Stream(device=dev, priority=like.priority)
-    return st
 
 
 def approximate_leverage_scores(
@@ -273,57 +246,4 @@ def non_causal_attn_scores(
         N.dtype_code(q.dtype), N.ptr(ws), ws.numel(), N.stream(dev),
     )
     N.check(rc, "cvllm_chunk_attn_scores")
-    return out
-
-
-def _chunk_scores_raw(q, k, cu_seqlens_qk, max_seqlen_qk, chunk_size, sm_scale):
-    """First half of non_causal_attn_scores on the CURRENT stream: per-key column sums + per-item partial
-    moments.  Returns the state the second half needs.  The partials live in a tensor of their own (not the
-    per-stream named workspace): the two halves run on different streams."""
-    Ntok, HQ, D = q.shape
-    HKV = k.shape[1]
-    assert HQ % HKV == 0 and q.stride(-1) == 1 and k.stride(-1) == 1 and q.stride(1) == D and k.stride(1) == D
-    B = cu_seqlens_qk.numel() - 1
-    dev = q.device
-    cu = cu_seqlens_qk.to(device=dev, dtype=torch.int32).contiguous()
-    out = torch.empty((Ntok, HKV), dtype=torch.float32, device=dev)
-    L = N.lib()
-    ws = torch.empty(L.cvllm_chunk_attn_scores_workspace_bytes(B, Ntok, HKV, int(chunk_size)), dtype=torch.uint8,
-                     device=dev)
-    rc = L.cvllm_chunk_attn_scores_raw(
-        N.ptr(q), N.ptr(k), q.stride(0), k.stride(0), N.ptr(cu), B, Ntok, HQ, HKV, D, int(chunk_size),
-        int(max_seqlen_qk), float(sm_scale), N.ptr(out), N.dtype_code(q.dtype), 1, N.ptr(ws), ws.numel(),
-        N.stream(dev))
-    N.check(rc, "cvllm_chunk_attn_scores_raw")
-    return out, ws, cu, B, HKV
-
-
-def _chunk_scores_finalize(state, raw_stream, cu_seqlens_qk, max_seqlen_qk, *, chunk_size, sm_scale=None,
-                           normalize=True, accum_scores=None, context_lens=None, protected_first_tokens=None,
-                           protected_last_tokens=None, accum_blending=None):
-    """Second half on the CURRENT stream, ordered behind `raw_stream`: z-score per sequence, + blend * accum,
-    protected first / last tokens <- +inf (compression/compactor.py:224-269,560-599)."""
-    out, ws, cu, B, HKV = state
-    dev = out.device
-    cur = torch.cuda.current_stream(dev)
-    cur.wait_stream(raw_stream)
-    out.record_stream(cur)
-    ws.record_stream(cur)
-    Ntok = out.shape[0]
-    pf = pl = None
-    if protected_first_tokens is not None or protected_last_tokens is not None:
-        pf_l = list(protected_first_tokens) if protected_first_tokens is not None else [0] * B
-        pl_l = list(protected_last_tokens) if protected_last_tokens is not None else [0] * B
-        both = _protected_counts(tuple(pf_l), tuple(pl_l), dev)
-        pf, pl = both[:B], both[B:]
-    blend = 1.0 if accum_blending is None else float(accum_blending)
-    acc_dtype, acc_stride = 2, 0
-    if accum_scores is not None:
-        assert accum_scores.shape == (Ntok, HKV) and accum_scores.stride(1) == 1
-        acc_dtype = 2 if accum_scores.dtype == torch.float32 else N.dtype_code(accum_scores.dtype)
-        acc_stride = accum_scores.stride(0)
-    rc = N.lib().cvllm_chunk_attn_scores_finalize(
-        N.ptr(cu), B, Ntok, HKV, int(chunk_size), int(max_seqlen_qk), int(bool(normalize)), N.ptr(accum_scores),
-        acc_dtype, acc_stride, blend, N.ptr(pf), N.ptr(pl), N.ptr(out), N.ptr(ws), ws.numel(), N.stream(dev))
-    N.check(rc, "cvllm_chunk_attn_scores_finalize")
     return out

@@ -517,7 +517,7 @@ using namespace cvllm;
 int cvllm_launch_chunk_scores_umma(const void* q, const void* k, int64_t q_stride_n, int64_t k_stride_n,
                                    const int32_t* cu, int B, int N, int HQ, int HKV, int chunk, int max_chunks,
                                    int n_ci, float scale_log2, float* raw, float* partials, bool bf16,
-                                   bool slim, cudaStream_t st);
+                                   cudaStream_t st);
 
 static size_t al256(size_t x) { return (x + 255) & ~(size_t)255; }
 static const int kScSmem = kKeyTile * kKRowBytes;  // 40 KB
@@ -528,15 +528,13 @@ extern "C" size_t cvllm_chunk_attn_scores_workspace_bytes(int B, int N, int HKV,
   return al256((size_t)B * max_chunks * HKV * 2 * sizeof(float));
 }
 
-// phases: 1 = column sums + per-item partials (reads q, k), 2 = z-score / blend / protection (reads accum), 3 = both;
-// | 4 = phase 1 with the small shared-memory footprint (runs beside other kernels' CTAs)
 static int chunk_scores_impl(const void* q, const void* k, int64_t q_stride_n, int64_t k_stride_n,
                              const int32_t* cu_seqlens, int B, int N, int HQ, int HKV, int D,
                              int chunk, int max_seqlen, float sm_scale, int normalize,
                              const void* accum, int accum_dtype, int64_t accum_stride_n,
                              float blend, const int32_t* prot_first, const int32_t* prot_last,
                              float* out, int dtype, void* workspace, size_t workspace_bytes,
-                             cvllm_stream_t stream, int phases) {
+                             cvllm_stream_t stream) {
   CVLLM_CHECK_ARG(B > 0 && N >= 0 && HQ > 0 && HKV > 0 && chunk > 0 && max_seqlen >= 0);
   if (N == 0 || max_seqlen == 0) return CVLLM_OK;
   CVLLM_CHECK_ARG(q && k && cu_seqlens && out && workspace);
@@ -557,13 +555,11 @@ static int chunk_scores_impl(const void* q, const void* k, int64_t q_stride_n, i
   p.scale_log2 = sm_scale * 1.4426950408889634f;
   const int64_t items = (int64_t)B * HKV * grid_chunks;
   CVLLM_CHECK_SUPPORTED(items < (1ll << 31));
-  if (!(phases & 1)) {
-    // finalize only: the column sums and partials of an earlier phase-1 call are in `out` / `workspace`
-  } else if (test_options().chunk_scores_v1.load() == 0) {
+  if (test_options().chunk_scores_v1.load() == 0) {
     // product path: tcgen05 tiles fed by TMA (score_chunk_umma.cu)
     const int rc = cvllm_launch_chunk_scores_umma(q, k, q_stride_n, k_stride_n, cu_seqlens, B, N, HQ, HKV, chunk,
                                                   max_chunks, grid_chunks, p.scale_log2, out, p.partials,
-                                                  dtype == CVLLM_BF16, (phases & 4) != 0, st);
+                                                  dtype == CVLLM_BF16, st);
     if (rc != CVLLM_OK) return rc;
   } else {
     const int grid = (int)(items < sm_count() ? items : sm_count());
@@ -578,7 +574,6 @@ static int chunk_scores_impl(const void* q, const void* k, int64_t q_stride_n, i
   f.out = out; f.partials = p.partials; f.cu = cu_seqlens; f.accum = accum; f.accum_dtype = accum_dtype;
   f.accum_stride_n = accum_stride_n; f.blend = blend; f.prot_first = prot_first; f.prot_last = prot_last;
   f.HKV = HKV; f.chunk = chunk; f.max_chunks = max_chunks; f.normalize = normalize;
-  if (!(phases & 2)) return CVLLM_OK;
   const int tiles = max(1, min((max_seqlen * HKV + 255) / 256, 2 * sm_count()));
   chunk_finalize_kernel<<<dim3(tiles, B), 256, 0, st>>>(f);
   CVLLM_CHECK_LAUNCH();
@@ -594,30 +589,7 @@ extern "C" int cvllm_chunk_attn_scores(const void* q, const void* k, int64_t q_s
                                        cvllm_stream_t stream) {
   return chunk_scores_impl(q, k, q_stride_n, k_stride_n, cu_seqlens, B, N, HQ, HKV, D, chunk, max_seqlen, sm_scale,
                            normalize, accum, accum_dtype, accum_stride_n, blend, prot_first, prot_last, out, dtype,
-                           workspace, workspace_bytes, stream, 3);
-}
-
-// The two halves of cvllm_chunk_attn_scores as separate calls, so the caller can put the q/k half on a stream of
-// its own: it does not depend on `accum` (the leverage scores), whose eigensolver is a 250 us latency chain that
-// leaves the SMs mostly idle.  Same arguments; `out` and `workspace` carry the state from phase 1 to phase 2.
-extern "C" int cvllm_chunk_attn_scores_raw(const void* q, const void* k, int64_t q_stride_n, int64_t k_stride_n,
-                                           const int32_t* cu_seqlens, int B, int N, int HQ, int HKV, int D,
-                                           int chunk, int max_seqlen, float sm_scale, float* out, int dtype,
-                                           int cotenant, void* workspace, size_t workspace_bytes,
-                                           cvllm_stream_t stream) {
-  return chunk_scores_impl(q, k, q_stride_n, k_stride_n, cu_seqlens, B, N, HQ, HKV, D, chunk, max_seqlen, sm_scale,
-                           0, nullptr, 2, 0, 1.0f, nullptr, nullptr, out, dtype, workspace, workspace_bytes, stream,
-                           cotenant ? 5 : 1);
-}
-
-extern "C" int cvllm_chunk_attn_scores_finalize(const int32_t* cu_seqlens, int B, int N, int HKV, int chunk,
-                                                int max_seqlen, int normalize, const void* accum, int accum_dtype,
-                                                int64_t accum_stride_n, float blend, const int32_t* prot_first,
-                                                const int32_t* prot_last, float* out, void* workspace,
-                                                size_t workspace_bytes, cvllm_stream_t stream) {
-  return chunk_scores_impl(out, out, 8, 8, cu_seqlens, B, N, HKV, HKV, 128, chunk, max_seqlen, 1.0f, normalize,
-                           accum, accum_dtype, accum_stride_n, blend, prot_first, prot_last, out, CVLLM_BF16,
-                           workspace, workspace_bytes, stream, 2);
+                           workspace, workspace_bytes, stream);
 }
 
 static void snap_geometry(int max_seqlen_k, int HQ, int HKV, int w, int* rows_pad, int* n_splits,

@@ -23,7 +23,7 @@ namespace cs {
 constexpr int kTile = 128, kHD = 128;
 constexpr int kTileBytes = kTile * kHD * 2;  // 32 KB
 constexpr int kBoxBytes = kTileBytes / 2;    // one [128 x 64] swizzled box
-constexpr int kMaxQSlots = 4;  // fat: 2 K buffers + 4 Q slots (192 KB); slim: 1 K buffer + 2 Q slots (96 KB)
+constexpr int kMaxQSlots = 4;  // 2 K buffers + 4 Q slots = 192 KB of tiles in flight per SM
 constexpr int kThreads = 384;                // 3 warpgroups
 constexpr int kRegsSoftmax = 224, kRegsOther = 56;
 constexpr int kRefBlockM = 64;               // the reference's only K11 config (compactor.py:338-347)
@@ -289,7 +289,7 @@ using namespace cvllm;
 int cvllm_launch_chunk_scores_umma(const void* q, const void* k, int64_t q_stride_n, int64_t k_stride_n,
                                    const int32_t* cu, int B, int N, int HQ, int HKV, int chunk, int max_chunks,
                                    int n_ci, float scale_log2, float* raw, float* partials, bool bf16,
-                                   bool slim, cudaStream_t st) {
+                                   cudaStream_t st) {
   CUtensorMap tm_q, tm_k;
   const uint32_t box[3] = {64, 1, (uint32_t)cs::kTile};
   const uint64_t dq[3] = {(uint64_t)cs::kHD, (uint64_t)HQ, (uint64_t)N};
@@ -303,10 +303,8 @@ int cvllm_launch_chunk_scores_umma(const void* q, const void* k, int64_t q_strid
   ChunkUmmaParams p;
   p.cu = cu; p.raw = raw; p.partials = partials; p.B = B; p.HKV = HKV; p.G = HQ / HKV; p.chunk = chunk;
   p.max_chunks = max_chunks; p.n_ci = n_ci; p.scale_log2 = scale_log2;
-  // slim: 96 KB of tiles, so the CTA shares its SM with the CTAs of the leverage chain it runs beside (three
-  // 40 KB eigensolver CTAs); fat: 192 KB in flight per SM, the standalone bandwidth configuration
-  p.k_bufs = slim ? 1 : 2;
-  p.q_slots = slim ? 2 : cs::kMaxQSlots;
+  p.k_bufs = 2;
+  p.q_slots = cs::kMaxQSlots;
   const int64_t items = (int64_t)B * HKV * n_ci;
   const int grid = (int)(items < sm_count() ? items : sm_count());
   const int smem = (p.k_bufs + p.q_slots) * cs::kTileBytes + (int)sizeof(ChunkUmmaSmem) + 1024;

@@ -334,24 +334,6 @@ int cvllm_chunk_attn_scores(const void* q, const void* k, int64_t q_stride_n,
                             void* workspace, size_t workspace_bytes,
                             cvllm_stream_t stream);
 
-/* The two halves of cvllm_chunk_attn_scores as separate calls (same arguments, `out` and `workspace` carry the
- * state): _raw reads q / k only (column sums + per-item partials), _finalize applies the z-score, the blend with
- * `accum` and the protection.  The reference runs both after the leverage scores on one stream
- * (compression/compactor.py:44-59); split, the q/k half can run on a stream of its own beside the leverage
- * chain's eigensolver.  cotenant != 0: size the CTAs (96 KB of tiles instead of 192 KB) to share their SMs with
- * the CTAs of the kernels they run beside. */
-int cvllm_chunk_attn_scores_raw(const void* q, const void* k, int64_t q_stride_n,
-                                int64_t k_stride_n, const int32_t* cu_seqlens, int B, int N,
-                                int HQ, int HKV, int D, int chunk, int max_seqlen,
-                                float sm_scale, float* out, int dtype, int cotenant,
-                                void* workspace, size_t workspace_bytes, cvllm_stream_t stream);
-int cvllm_chunk_attn_scores_finalize(const int32_t* cu_seqlens, int B, int N, int HKV, int chunk,
-                                     int max_seqlen, int normalize, const void* accum,
-                                     int accum_dtype, int64_t accum_stride_n, float blend,
-                                     const int32_t* prot_first, const int32_t* prot_last,
-                                     float* out, void* workspace, size_t workspace_bytes,
-                                     cvllm_stream_t stream);
-
 /* query_aware_key_scores — compression/snapkv.py:39-276,332-448.  SnapKV:
  * last-w queries x G heads against keys [0, L-w), softmax over those keys,
  * column sums, causal `kpool`-tap mean pool inside `pool_segment`-key

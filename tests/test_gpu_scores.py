@@ -344,10 +344,9 @@ def test_leverage_one_token_chunk_is_nan():
     assert torch.isnan(out[512]).all() and torch.isfinite(out[:512]).all()
 
 
-def test_plugin_split_scoring_equals_single_call():
-    """CompactorCompression.post_rope_scoring runs the q/k half of the chunk scorer on a second side stream
-    beside the leverage chain and the epilogue behind it (cvllm_chunk_attn_scores_raw / _finalize): same bits as
-    the single-stream call, with and without a store stream, twice in a row (workspace reuse)."""
+def test_plugin_scoring_is_stream_independent():
+    """CompactorCompression.pre/post_rope_scoring on the caller's stream, on a high-priority store stream and on
+    a default-priority one: same bits, twice in a row (per-stream workspace reuse)."""
     from compactor_vllm.compression.compactor import CompactorCompression
     from compactor_vllm.compression.compression_config import CompressionMethod
     from compactor_vllm.utils.arguments import max_tokens_to_retain, tokens_to_retain

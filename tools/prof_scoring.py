@@ -30,16 +30,13 @@ def main():
                              k_cache=w.attn.k_cache, v_cache=w.attn.v_cache, page_table=w.attn.page_table,
                              bh_lens=lens, batch_mapping=w.batch_mapping, PAGE_SIZE=bench.PS)
 
-    from compactor_vllm.compression.compactor import _chunk_scores_raw, non_causal_attn_scores
+    from compactor_vllm.compression.compactor import non_causal_attn_scores
 
     def chunk_fat():
         return non_causal_attn_scores(w.q, w.k, w.v, w.cu, w.n_tok, 128, sm_scale=1.0, normalize=True)
 
-    def chunk_slim_raw():
-        return _chunk_scores_raw(w.q, w.k, w.cu, w.n_tok, 128, 1.0)
-
-    stages = {"compactor_chain": w.compress_only, "chunk_scores_fat(+finalize)": chunk_fat,
-              "chunk_scores_slim(raw)": chunk_slim_raw, "snapkv": snap, "store_all": store_all}
+    stages = {"compactor_chain": w.compress_only, "chunk_scores(+finalize)": chunk_fat, "snapkv": snap,
+              "store_all": store_all}
     for name, fn in stages.items():
         try:
             once = "--once" in sys.argv  # under ncu --set full: one warm-up pass + one pass per stage
