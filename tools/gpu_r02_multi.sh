@@ -5,8 +5,8 @@ N=${1:-2}
 mkdir -p gpurun_out
 run() { python -m torch.distributed.run --nnodes=1 --nproc-per-node $1 --master-addr 127.0.0.1 --master-port $2 "${@:3}"; }
 nvidia-smi topo -m > gpurun_out/topo_n$N.txt 2>&1
-for n in $(seq 2 $N); do
-  case $n in 2|4|8) ;; *) continue;; esac
+for n in ${2:-2} ${3:-} ${4:-}; do
+  [ "$n" -le "$N" ] || continue
   timeout 600 bash -c "$(declare -f run); run $n 2951$n tools/tp_allreduce_check.py" > gpurun_out/tp_allreduce_sys_n$n.json 2> gpurun_out/tp_allreduce_sys_n$n.err
   echo "allreduce sys n=$n rc=$?"; python - <<PY
 import json
@@ -16,7 +16,7 @@ try:
 except Exception as ex:
     print(' parse failed', ex)
 PY
-  CVLLM_LIB=compactor-vllm_b200/lib/variants/lib_arrelaxed.so timeout 600 bash -c "$(declare -f run); run $n 2952$n tools/tp_allreduce_check.py" > gpurun_out/tp_allreduce_relaxed_n$n.json 2> gpurun_out/tp_allreduce_relaxed_n$n.err
+  [ "$n" -eq "$N" ] && CVLLM_LIB=compactor-vllm_b200/lib/variants/lib_arrelaxed.so timeout 600 bash -c "$(declare -f run); run $n 2952$n tools/tp_allreduce_check.py" > gpurun_out/tp_allreduce_relaxed_n$n.json 2> gpurun_out/tp_allreduce_relaxed_n$n.err
   echo "allreduce relaxed n=$n rc=$?"
   timeout 900 bash -c "$(declare -f run); run $n 2953$n bench.py --gpus $n --steps 10 --warmup 3" > gpurun_out/bench_n$n.json 2> gpurun_out/bench_n$n.err
   echo "bench n=$n rc=$?"; tail -c 3000 gpurun_out/bench_n$n.json; tail -3 gpurun_out/bench_n$n.err
