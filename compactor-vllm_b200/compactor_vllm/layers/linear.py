@@ -37,18 +37,19 @@ class PeerAllReduce:
         assert self.world <= 8
         self.device = device or torch.device("cuda", torch.cuda.current_device())
         # One-shot reads (world-1) x message per rank, two-shot 2 x (world-1)/world x message plus one publishing
-        # barrier; every barrier is a system-scope release / acquire pair (csrc/allreduce.cu).  Switch points measured
-        # on one 8 x B200 box (profiles/r01h_tp_allreduce_n8.json, re-checked in profiles/r02_tp_allreduce*.json).
-        # Measured per call inside a CUDA graph, [rows, 8192] bf16 (profiles/r01h_tp_allreduce*.json):
-        #   8 ranks: one-shot 7.8 / 10.6 / 19.2 us at 16 KB / 256 KB / 1 MB, two-shot 11.8 / 13.6 / 14.9 us -> switch
-        #            at 512 KB; 4 MB: 21.3 us (NCCL 56.0), 8 MB: 33.5 us (NCCL 73.1)
-        #   4 ranks: one-shot 12.3 / 17.6 us at 1 / 2 MB, two-shot 13.4 / 15.3 us -> switch at 1.5 MB; 8 MB 30.9 (NCCL 49.7)
-        #   2 ranks: both forms move the same bytes, the one-shot has one barrier less -> never two-shot
+        # barrier; every barrier is a system-scope release / acquire pair (csrc/allreduce.cu).  Measured per call
+        # inside a CUDA graph, [rows, 8192] bf16, on one 8 x B200 box (profiles/r02f_tp_allreduce_sys_n{2,4,8}.json;
+        # the relaxed-flag build of round 1 is 4-8 us faster per call, profiles/r02f_tp_allreduce_relaxed_n8.json):
+        #   8 ranks: one-shot 12.8 / 18.8 / 26.7 / 38.5 us at 16 KB / 256 KB / 1 MB / 2 MB, two-shot 16.9 / 22.0 /
+        #            26.6 / 28.3 us -> switch at 1 MB; 4 MB: 32.6 us (NCCL 55.9), 8 MB: 44.4 us (NCCL 73.2);
+        #            NCCL at 16 KB .. 2 MB: 27.4 / 30.7 / 31.3 / 35.2 us
+        #   4 ranks: one-shot 24.9 / 35.2 us at 2 / 4 MB, two-shot 25.7 / 31.2 us -> switch at 3 MB; 8 MB 41.6 (NCCL 49.0)
+        #   2 ranks: both forms move the same bytes, the one-shot has one barrier less -> never two-shot; with the
+        #            formal fences the one-shot only ties NCCL there (11.0 / 15.5 / 17.7 us vs 13.6 / 15.7 / 17.7)
         if max_bytes is None:
             max_bytes = 8 << 20
         if twoshot_min_bytes is None:
-            twoshot_min_bytes = ((512 << 10) if self.world >= 8 else (1536 << 10) if self.world >= 4
-                                 else (4 << 20) if self.world == 3 else (1 << 62))
+            twoshot_min_bytes = ((1 << 20) if self.world >= 8 else (3 << 20) if self.world >= 3 else (1 << 62))
         self.max_bytes = int(max_bytes)
         self.twoshot_min_bytes = int(twoshot_min_bytes)
         lib = N.lib()
