@@ -27,7 +27,7 @@ namespace cvllm {
 
 constexpr int kLevThreads = 256;
 constexpr int kSk = 48;            // sketch columns
-constexpr int kTokTile = 256;      // tokens per smem tile
+constexpr int kTokTile = 512;      // tokens per smem tile: the engine's chunk (512) is resident, one sketch pass
 constexpr int kXtStride = kTokTile + 8;  // 16-bit elements per sketch row (pad: bank spread)
 
 struct LevParams {
@@ -40,6 +40,7 @@ struct LevParams {
   float* gram;      // [n_chunks*HKV][48][48] fp32
   float* mean;      // [n_chunks*HKV][48] fp32
   float* sv;        // [n_chunks*HKV][48][48] fp32 (values rounded to 16-bit)
+  uint16_t* xc;     // centred sketch, 16-bit: chunk ch / head h at (c_beg*HKV + h*c_len)*48, [48][c_len] sketch-major
   int HKV;
   float reg;
 };
@@ -172,21 +173,44 @@ __global__ void __launch_bounds__(kLevThreads, 2) leverage_gram_kernel(const Lev
   // ---- pass B: Gram of the centred sketch, G[i][j] = sum_t xc[t][i] xc[t][j] ----
   for (int t0 = 0; t0 < c_len; t0 += kTokTile) {
     const int nt = min(kTokTile, c_len - t0);
-    // one tile and the uncentred sketch is still resident: centre it in place
-    if (c_len <= kTokTile) {
-      for (int i = tid; i < kSk * nt; i += kLevThreads) {
-        const int c = i / nt, t = i - c * nt;
-        sm.xt[c][t] = to16<BF16>(round16<BF16>(from16<BF16>(sm.xt[c][t]) - sm.mean[c]));
-      }
-    } else {
+    // Centre (one tile: the uncentred sketch is still resident; several tiles: re-derived centred), zero the
+    // padded token columns (partial k16 steps must contribute nothing) and hand the centred sketch to the score
+    // kernel — one vectorised pass, a warp per sketch row, 8 tokens per lane.  (A flat `i / nt` element loop
+    // here was 65 % of the kernel's instructions: ncu r02g.)
+    const bool resident = c_len <= kTokTile;
+    if (!resident) {
       sketch_tile<BF16>(sm, p, h, c_beg + t0, nt, true);
+      __syncthreads();
     }
-    __syncthreads();
-    // zero the padded token columns so partial k16 steps contribute nothing
     const int nt16 = (nt + 15) & ~15;
-    for (int i = tid; i < kSk * (nt16 - nt); i += kLevThreads) {
-      const int c = i / (nt16 - nt), t = nt + i % (nt16 - nt);
-      sm.xt[c][t] = 0;
+    {
+      uint16_t* xc = p.xc + ((int64_t)c_beg * p.HKV + (int64_t)h * c_len) * kSk;
+      const bool vec_ok = (c_len & 7) == 0;
+      for (int c = warp; c < kSk; c += kLevThreads / 32) {
+        const float mu = resident ? sm.mean[c] : 0.f;
+        for (int t8 = lane * 8; t8 < nt16; t8 += 256) {
+          uint4 v = *reinterpret_cast<const uint4*>(&sm.xt[c][t8]);
+          uint32_t w4[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            float lo = from16<BF16>((uint16_t)(w4[e] & 0xffffu)), hi = from16<BF16>((uint16_t)(w4[e] >> 16));
+            if (resident) { lo = round16<BF16>(lo - mu); hi = round16<BF16>(hi - mu); }
+            const uint32_t blo = (t8 + 2 * e < nt) ? to16<BF16>(lo) : 0u;
+            const uint32_t bhi = (t8 + 2 * e + 1 < nt) ? to16<BF16>(hi) : 0u;
+            w4[e] = blo | (bhi << 16);
+          }
+          v = make_uint4(w4[0], w4[1], w4[2], w4[3]);
+          *reinterpret_cast<uint4*>(&sm.xt[c][t8]) = v;
+          uint16_t* dst = xc + (int64_t)c * c_len + t0 + t8;
+          if (vec_ok && t8 + 8 <= nt) {
+            *reinterpret_cast<uint4*>(dst) = v;
+          } else {
+#pragma unroll
+            for (int e = 0; e < 8; ++e)
+              if (t8 + e < nt) dst[e] = (uint16_t)(w4[e >> 1] >> ((e & 1) * 16));
+          }
+        }
+      }
     }
     __syncthreads();
     const int r = lane >> 2, j = lane & 3;
@@ -587,36 +611,76 @@ __global__ void __launch_bounds__(kLevThreads, 2) leverage_score_kernel(const Le
   const int c_beg = p.chunk_offsets[ch], c_len = p.chunk_offsets[ch + 1] - c_beg;
   if (c_len <= 0) return;
   const int tid = threadIdx.x;
-  if (!p.sketch) load_phi(sm, p);
   {
     const float* svin = p.sv + (int64_t)(ch * p.HKV + h) * kSk * kSk;
     for (int i = tid; i < kSk * kSk; i += kLevThreads) (&sm.sv[0][0])[i] = svin[i];
     if (tid < kSk) sm.mean[tid] = p.mean[(int64_t)(ch * p.HKV + h) * kSk + tid];
   }
   __syncthreads();
+  // B fragments of U = Xc . SV (k = sketch column c, n = eigen-column): SV's entries are 16-bit values held in fp32
+  const int warp = tid >> 5, lane = tid & 31, r = lane >> 2, j = lane & 3;
+  uint32_t bfr[3][6][2];
+#pragma unroll
+  for (int ks = 0; ks < 3; ++ks)
+#pragma unroll
+    for (int nn = 0; nn < 6; ++nn) {
+      bfr[ks][nn][0] = pack2<BF16>(sm.sv[16 * ks + 2 * j][nn * 8 + r], sm.sv[16 * ks + 2 * j + 1][nn * 8 + r]);
+      bfr[ks][nn][1] = pack2<BF16>(sm.sv[16 * ks + 8 + 2 * j][nn * 8 + r], sm.sv[16 * ks + 9 + 2 * j][nn * 8 + r]);
+    }
+  const bool vec_ok = (c_len & 7) == 0;
   for (int t0 = 0; t0 < c_len; t0 += kTokTile) {
     const int nt = min(kTokTile, c_len - t0);
-    sketch_tile<BF16>(sm, p, h, c_beg + t0, nt, true);
-    __syncthreads();
-    for (int t = tid; t < nt; t += kLevThreads) {
-      float x[kSk];
+    {
+      const uint16_t* xc = p.xc + ((int64_t)c_beg * p.HKV + (int64_t)h * c_len) * kSk;
+      for (int c = warp; c < kSk; c += kLevThreads / 32) {
+        const uint16_t* src = xc + (int64_t)c * c_len + t0;
+        for (int t8 = lane * 8; t8 < nt; t8 += 256) {
+          if (vec_ok) {
+            *reinterpret_cast<uint4*>(&sm.xt[c][t8]) = *reinterpret_cast<const uint4*>(src + t8);
+          } else {
 #pragma unroll
-      for (int c = 0; c < kSk; ++c) x[c] = from16<BF16>(sm.xt[c][t]);
-      float score = 0.f;
-#pragma unroll 4
-      for (int jc = 0; jc < kSk; jc += 4) {
-        float u0 = 0.f, u1 = 0.f, u2 = 0.f, u3 = 0.f;
-#pragma unroll
-        for (int c = 0; c < kSk; ++c) {
-          const float4 s4 = *reinterpret_cast<const float4*>(&sm.sv[c][jc]);
-          u0 = fmaf(x[c], s4.x, u0); u1 = fmaf(x[c], s4.y, u1);
-          u2 = fmaf(x[c], s4.z, u2); u3 = fmaf(x[c], s4.w, u3);
+            for (int e = 0; e < 8; ++e) sm.xt[c][t8 + e] = (t8 + e < nt) ? src[t8 + e] : (uint16_t)0;
+          }
         }
-        u0 = round16<BF16>(u0); u1 = round16<BF16>(u1); u2 = round16<BF16>(u2); u3 = round16<BF16>(u3);
-        score += round16<BF16>(u0 * u0) + round16<BF16>(u1 * u1) + round16<BF16>(u2 * u2) +
-                 round16<BF16>(u3 * u3);
       }
-      p.raw[(int64_t)(c_beg + t0 + t) * p.HKV + h] = fmaxf(round16<BF16>(score), 0.f);
+    }
+    __syncthreads();
+    // U[16 tokens x 48] per m-tile on mma.sync (the scalar form was 48 x 48 FFMA per token); the A operand is read
+    // straight out of the sketch-major tile with ldmatrix.trans
+    const int n_mt = (nt + 15) / 16;
+    for (int mt = warp; mt < n_mt; mt += kLevThreads / 32) {
+      float acc[6][4];
+#pragma unroll
+      for (int nn = 0; nn < 6; ++nn) acc[nn][0] = acc[nn][1] = acc[nn][2] = acc[nn][3] = 0.f;
+#pragma unroll
+      for (int ks = 0; ks < 3; ++ks) {
+        const int mid = lane >> 3;  // 8x8 matrix this lane addresses: (k half, token half)
+        const uint16_t* rowp = &sm.xt[16 * ks + (mid >> 1) * 8 + (lane & 7)][mt * 16 + (mid & 1) * 8];
+        uint32_t a0, a1, a2, a3;
+        asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+                     : "=r"(a0), "=r"(a1), "=r"(a2), "=r"(a3)
+                     : "r"(static_cast<uint32_t>(__cvta_generic_to_shared(rowp))));
+#pragma unroll
+        for (int nn = 0; nn < 6; ++nn) mma16816<BF16>(acc[nn], a0, a1, a2, a3, bfr[ks][nn][0], bfr[ks][nn][1]);
+      }
+      // score = round16(sum_j round16(round16(u_j)^2)) (compactor.py:209-210), rows r and r + 8 of the m-tile
+      float s_lo = 0.f, s_hi = 0.f;
+#pragma unroll
+      for (int nn = 0; nn < 6; ++nn) {
+        const float u0 = round16<BF16>(acc[nn][0]), u1 = round16<BF16>(acc[nn][1]);
+        const float u2 = round16<BF16>(acc[nn][2]), u3 = round16<BF16>(acc[nn][3]);
+        s_lo += round16<BF16>(u0 * u0) + round16<BF16>(u1 * u1);
+        s_hi += round16<BF16>(u2 * u2) + round16<BF16>(u3 * u3);
+      }
+      s_lo += __shfl_xor_sync(0xffffffffu, s_lo, 1);
+      s_lo += __shfl_xor_sync(0xffffffffu, s_lo, 2);
+      s_hi += __shfl_xor_sync(0xffffffffu, s_hi, 1);
+      s_hi += __shfl_xor_sync(0xffffffffu, s_hi, 2);
+      if (j == 0) {
+        const int t_lo = mt * 16 + r, t_hi = t_lo + 8;
+        if (t_lo < nt) p.raw[(int64_t)(c_beg + t0 + t_lo) * p.HKV + h] = fmaxf(round16<BF16>(s_lo), 0.f);
+        if (t_hi < nt) p.raw[(int64_t)(c_beg + t0 + t_hi) * p.HKV + h] = fmaxf(round16<BF16>(s_hi), 0.f);
+      }
     }
     __syncthreads();
   }
@@ -678,7 +742,7 @@ extern "C" size_t cvllm_leverage_scores_workspace_bytes(int N, int HKV, int sket
   if (N <= 0 || HKV <= 0) return 256;
   const size_t mats = (size_t)(n_chunks > 0 ? n_chunks : 0) * HKV;
   return lev_align((size_t)N * HKV * sizeof(float)) + 2 * lev_align(mats * kSk * kSk * sizeof(float)) +
-         lev_align(mats * kSk * sizeof(float));
+         lev_align(mats * kSk * sizeof(float)) + lev_align((size_t)N * HKV * kSk * sizeof(uint16_t));
 }
 
 static int leverage_launch(const void* k_pre, int64_t k_stride_n, int64_t k_stride_h, const void* sketch_rows,
@@ -706,6 +770,8 @@ static int leverage_launch(const void* k_pre, int64_t k_stride_n, int64_t k_stri
   p.sv = reinterpret_cast<float*>(wsb);
   wsb += lev_align(mats * kSk * kSk * sizeof(float));
   p.mean = reinterpret_cast<float*>(wsb);
+  wsb += lev_align(mats * kSk * sizeof(float));
+  p.xc = reinterpret_cast<uint16_t*>(wsb);
   const size_t smem = sizeof(LevSmem);
   static std::atomic<uint64_t> attr_g[2] = {{0}, {0}}, attr_s[2] = {{0}, {0}};
   const dim3 grid(n_chunks, HKV);
