@@ -1,4 +1,5 @@
-"""A handful of decode launches (B=16 ragged, mean 10240 rows/head: BASELINE config 3's shape) for ncu."""
+"""A handful of decode launches for ncu: B=16 at the metric's shape (16432 rows per head = 32K context, 50 % keep;
+default) or `cfg3` = B=16 ragged, mean 10240 rows/head (BASELINE config 3)."""
 import sys
 from pathlib import Path
 ROOT = Path(__file__).resolve().parent.parent
@@ -11,7 +12,10 @@ dev = torch.device("cuda", 0)
 torch.cuda.set_device(dev)
 B, mean = 16, 10240
 gd = torch.Generator().manual_seed(11 + B)
-lens_bh = torch.randint(mean // 2, mean * 3 // 2 + 1, (B, HKV), generator=gd).to(torch.int32)
+if len(sys.argv) > 1 and sys.argv[1] == "cfg3":
+    lens_bh = torch.randint(mean // 2, mean * 3 // 2 + 1, (B, HKV), generator=gd).to(torch.int32)
+else:
+    lens_bh = torch.full((B, HKV), 16432, dtype=torch.int32)
 kc, vc, pt, bm = _paged(torch, B, int(lens_bh.max()) + 64, 12 + B, dev)
 ld = lens_bh.to(dev)
 q = torch.randn((B, HQ, D), device=dev, dtype=torch.bfloat16)

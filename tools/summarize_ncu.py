@@ -80,7 +80,9 @@ if __name__ == "__main__":
             {"command": "ncu --set full --clock-control none -k regex:prefill_attn -s 3 -c 1 python bench.py --steps 2 --warmup 3 --no-extras --no-cpu",
              "algorithmic_bytes": 32768 * (32 + 16) * 128 * 2 + 32768 * 32 * 128 * 2})
     capture(prefix, "prof_decode", "decode_traffic",
-            {"command": "ncu --set full --clock-control none -k regex:decode_attn -s 4 -c 1 python tools/prof_decode.py"})
+            {"command": "ncu --set full --clock-control none -k regex:decode_attn -s 4 -c 1 python tools/prof_decode.py "
+                        "(B=16 x 8 heads x 16432 rows: the metric's 32K x 50 % shape)",
+             "algorithmic_bytes": 16 * 8 * 16432 * 512 + 16 * 32 * 128 * 2 * 2})
     capture(prefix, "prof_rope", "rope_traffic",
             {"command": "ncu --set full --clock-control none -k regex:rope_qk -s 8 -c 1 python tools/probe_rope.py (plain rope, 32768 tokens)",
              "algorithmic_bytes": 32768 * 40 * 128 * 2 * 2})
