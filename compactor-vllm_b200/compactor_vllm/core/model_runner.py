@@ -34,6 +34,26 @@ def _pad_batch(n: int) -> int:
     return b
 
 
+def _check_shape_envelope(hf, config: LLMConfig) -> None:
+    """Fail at construction, with the reason, for geometries the sm_100a kernels do not serve (INTEGRATION.md
+    section 3: the per-call answer would be CVLLM_E_UNSUPPORTED in the middle of the first prefill)."""
+    head_dim = getattr(hf, "head_dim", None) or hf.hidden_size // hf.num_attention_heads
+    group = hf.num_attention_heads // hf.num_key_value_heads
+    problems = []
+    if head_dim != 128:
+        problems.append(f"head_dim {head_dim} (only 128)")
+    if group > 8:
+        problems.append(f"GQA group {group} (decode serves <= 8)")
+    if hf.num_key_value_heads > 16:
+        problems.append(f"{hf.num_key_value_heads} KV heads per rank (selection serves <= 16)")
+    if config.kvcache_page_size % 128 != 0:
+        problems.append(f"kvcache_page_size {config.kvcache_page_size} (prefill needs a multiple of 128)")
+    if config.leverage_sketch_size != 48:
+        problems.append(f"leverage_sketch_size {config.leverage_sketch_size} (only 48)")
+    if problems:
+        raise ValueError("model / config outside the kernels' shape envelope: " + "; ".join(problems))
+
+
 class KVCacheExhausted(RuntimeError):
     """The paged cache cannot hold the tokens a decode wave may still produce."""
 
@@ -45,6 +65,7 @@ class ModelRunner:
         assert torch.cuda.is_available(), "no CPU fallback"
         self.config = config
         hf = config.hf_config
+        _check_shape_envelope(hf, config)
         self.device = torch.device("cuda", torch.cuda.current_device())
         self.dtype = hf.torch_dtype if isinstance(hf.torch_dtype, torch.dtype) else torch.bfloat16
         kind = "qwen3" if "qwen3" in str(getattr(hf, "model_type", "llama")).lower() else "llama"

@@ -91,3 +91,21 @@ def test_slot_map_reuses_and_releases():
     assert [slots.acquire(cache, s) for s in (10, 11, 10, 12, 13)] == [1, 2, 1, 3, None]
     slots.release(cache, 11)
     assert cache.freed == [2] and 11 not in slots.by_seq
+
+
+def test_shape_envelope_is_checked_at_construction():
+    """D != 128 etc. are refused by name before any kernel is launched."""
+    from types import SimpleNamespace as NS
+
+    from compactor_vllm.core.model_runner import _check_shape_envelope
+
+    cfg = NS(kvcache_page_size=128, leverage_sketch_size=48)
+    _check_shape_envelope(NS(head_dim=128, hidden_size=4096, num_attention_heads=32, num_key_value_heads=8), cfg)
+    _check_shape_envelope(NS(head_dim=None, hidden_size=8192, num_attention_heads=64, num_key_value_heads=8), cfg)
+    with pytest.raises(ValueError, match="head_dim 64"):
+        _check_shape_envelope(NS(head_dim=64, hidden_size=2048, num_attention_heads=32, num_key_value_heads=8), cfg)
+    with pytest.raises(ValueError, match="GQA group 16"):
+        _check_shape_envelope(NS(head_dim=128, hidden_size=4096, num_attention_heads=32, num_key_value_heads=2), cfg)
+    with pytest.raises(ValueError, match="page_size 64"):
+        _check_shape_envelope(NS(head_dim=128, hidden_size=4096, num_attention_heads=32, num_key_value_heads=8),
+                              NS(kvcache_page_size=64, leverage_sketch_size=48))
