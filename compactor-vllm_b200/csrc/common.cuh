@@ -84,6 +84,7 @@ struct TestOptions {
   std::atomic<int> decode_mode{0};            // decode_attn.cu profiling modes (0 = product)
   std::atomic<int> decode_slots{0};           // >= 2: cap the decode TMA ring depth
   std::atomic<int> eig_trace{0};
+  std::atomic<int> snap_v1{0};                // 1: the mma.sync SnapKV kernels
   std::atomic<int> chunk_scores_v1{0};        // 1: the mma.sync chunk scorer (A/B against the tcgen05 one)
 };
 TestOptions& test_options();

@@ -519,6 +519,12 @@ int cvllm_launch_chunk_scores_umma(const void* q, const void* k, int64_t q_strid
                                    int n_ci, float scale_log2, float* raw, float* partials, bool bf16,
                                    cudaStream_t st);
 
+size_t cvllm_snap_umma_workspace_bytes(int B, int max_seqlen_k, int HKV);
+int cvllm_launch_snap_umma(const void* q, const void* k, int64_t q_stride_n, int64_t k_stride_n,
+                           const int32_t* cu_q, const int32_t* cu_k, int w, int B, int Nq, int Nk, int HQ, int HKV,
+                           int max_seqlen_k, float scale_log2, int kpool, int pool_segment, float* out, float* stats,
+                           bool bf16, cudaStream_t st);
+
 static size_t al256(size_t x) { return (x + 255) & ~(size_t)255; }
 static const int kScSmem = kKeyTile * kKRowBytes;  // 40 KB
 
@@ -608,7 +614,9 @@ extern "C" size_t cvllm_snapkv_scores_workspace_bytes(int B, int N, int HQ, int 
   if (B <= 0 || N <= 0 || HKV <= 0 || HQ <= 0) return 256;
   int rows_pad, n_splits, kps;
   snap_geometry(N, HQ, HKV, w, &rows_pad, &n_splits, &kps);
-  return al256((size_t)B * HKV * n_splits * rows_pad * 2 * sizeof(float));
+  const size_t v1 = (size_t)B * HKV * n_splits * rows_pad * 2 * sizeof(float);
+  const size_t v2 = cvllm_snap_umma_workspace_bytes(B, N, HKV);  // tcgen05 route (w * G <= 128)
+  return al256(v1 > v2 ? v1 : v2);
 }
 
 extern "C" int cvllm_snapkv_scores(const void* q, const void* k, int64_t q_stride_n, int64_t k_stride_n,
@@ -625,6 +633,14 @@ extern "C" int cvllm_snapkv_scores(const void* q, const void* k, int64_t q_strid
   CVLLM_CHECK_SUPPORTED(w * (HQ / HKV) <= 256);
   CVLLM_CHECK_ALIGN(aligned16(q) && aligned16(k) && q_stride_n % 8 == 0 && k_stride_n % 8 == 0);
   CVLLM_CHECK_ARG(workspace_bytes >= cvllm_snapkv_scores_workspace_bytes(B, max_seqlen_k, HQ, HKV, w));
+  if (w > 0 && w * (HQ / HKV) <= 128 && test_options().snap_v1.load() == 0) {
+    // product path for the engine's window (w = 32, G <= 4): tcgen05 tiles fed by TMA (score_snap_umma.cu).
+    // Nq: the q tensor has at least cu_seqlens_q[B] = Nk rows on the prefill path (queries and keys are the same tokens)
+    return cvllm_launch_snap_umma(q, k, q_stride_n, k_stride_n, cu_seqlens_q, cu_seqlens_k, w, B, Nk, Nk, HQ, HKV,
+                                  max_seqlen_k, sm_scale * 1.4426950408889634f, kpool, pool_segment, out,
+                                  reinterpret_cast<float*>(workspace), dtype == CVLLM_BF16,
+                                  static_cast<cudaStream_t>(stream));
+  }
   SnapParams p;
   p.q = q; p.k = k; p.q_stride_n = q_stride_n; p.k_stride_n = k_stride_n;
   p.cu_q = cu_seqlens_q; p.cu_k = cu_seqlens_k; p.stats = reinterpret_cast<float*>(workspace); p.out = out;
