@@ -279,23 +279,23 @@ prefill_attn2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
           if (c > row) s[c] = -INFINITY;
       }
 
-      float mx0 = s[0], mx1 = s[1], mx2 = s[2], mx3 = s[3];
+      auto row_max = [&]() -> float {
+        float mx0 = s[0], mx1 = s[1], mx2 = s[2], mx3 = s[3];
 #pragma unroll
-      for (int c = 4; c < kBN; c += 4) {
-        mx0 = fmaxf(mx0, s[c]);
-        mx1 = fmaxf(mx1, s[c + 1]);
-        mx2 = fmaxf(mx2, s[c + 2]);
-        mx3 = fmaxf(mx3, s[c + 3]);
-      }
-      const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
-      const float m_new = fmaxf(m_ref, mx * p.scale_log2);
-      const bool need = (j == 0) || (m_new > m_ref + p.rescale_threshold);
-      if (__any_sync(0xffffffffu, need)) {
-        const float alpha = ex2(m_ref - m_new);  // m_ref == -inf on the first tile -> 0
-        m_ref = m_new;
+        for (int c = 4; c < kBN; c += 4) {
+          mx0 = fmaxf(mx0, s[c]);
+          mx1 = fmaxf(mx1, s[c + 1]);
+          mx2 = fmaxf(mx2, s[c + 2]);
+          mx3 = fmaxf(mx3, s[c + 3]);
+        }
+        return fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3)) * p.scale_log2;
+      };
+      // O *= alpha, l *= alpha, m_ref <- m_to.  O holds PV(0..j-1); PV(j-1) may still be in flight.
+      auto rescale_to = [&](float m_to) {
+        const float alpha = ex2(m_ref - m_to);  // m_ref == -inf on the first tile -> 0
+        m_ref = m_to;
         l *= alpha;
         if (j > 0) {
-          // O holds PV(0..j-1); PV(j-1) may still be in flight
           mbar_wait(&sm.o_done[t], (j - 1) & 1);
           tc_fence_after();
 #pragma unroll
@@ -308,48 +308,42 @@ prefill_attn2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
             tmem_st32(o_tmem + c * 32, o);
           }
         }
-      }
+      };
+      // P = exp2(S*scale - m_ref) packed to 16 bit over the S columns; returns the row sum of this tile.
+      // Packed fp32 pairs: one FFMA2 scales and shifts two logits, one FADD2 adds two probabilities (A/B on B200,
+      // r02d: 7.62-7.68 ms vs 7.95-8.05 ms scalar at 32K).
+      auto write_p = [&]() -> float {
+        const float neg_m = (m_ref == -INFINITY) ? 0.f : -m_ref;
+        const float2 sc2 = make_float2(p.scale_log2, p.scale_log2), nm2 = make_float2(neg_m, neg_m);
+        float2 l2a = make_float2(0.f, 0.f), l2b = make_float2(0.f, 0.f);
+#pragma unroll
+        for (int c = 0; c < kBN / 32; ++c) {
+          uint32_t pk[16];
+#pragma unroll
+          for (int i = 0; i < 16; i += 2) {
+            const float2 t0 = __ffma2_rn(make_float2(s[c * 32 + 2 * i], s[c * 32 + 2 * i + 1]), sc2, nm2);
+            const float2 t1 = __ffma2_rn(make_float2(s[c * 32 + 2 * i + 2], s[c * 32 + 2 * i + 3]), sc2, nm2);
+            const float2 e0 = make_float2(ex2(t0.x), ex2(t0.y)), e1 = make_float2(ex2(t1.x), ex2(t1.y));
+            l2a = __fadd2_rn(l2a, e0);
+            l2b = __fadd2_rn(l2b, e1);
+            pk[i] = pack2<BF16>(e0.x, e0.y);
+            pk[i + 1] = pack2<BF16>(e1.x, e1.y);
+          }
+          tmem_st16(s_tmem + c * 16, pk);
+        }
+        return (l2a.x + l2b.x) + (l2a.y + l2b.y);
+      };
 
-      // ---- P = exp2(S*scale - m_ref), row sum, 16-bit pack, back to TMEM over S ----
-      const float neg_m = (m_ref == -INFINITY) ? 0.f : -m_ref;
-#ifndef CVLLM_PREFILL_SCALAR_SOFTMAX  // A/B on B200 (r02d): packed 7.62-7.68 ms vs scalar 7.95-8.05 ms at 32K
-      // packed fp32 pairs: one FFMA2 scales and shifts two logits, one FADD2 adds two probabilities to the row sum
-      // (half the FMA-pipe issue slots of the scalar form; same roundings)
-      const float2 sc2 = make_float2(p.scale_log2, p.scale_log2), nm2 = make_float2(neg_m, neg_m);
-      float2 l2a = make_float2(0.f, 0.f), l2b = make_float2(0.f, 0.f);
-#pragma unroll
-      for (int c = 0; c < kBN / 32; ++c) {
-        uint32_t pk[16];
-#pragma unroll
-        for (int i = 0; i < 16; i += 2) {
-          const float2 t0 = __ffma2_rn(make_float2(s[c * 32 + 2 * i], s[c * 32 + 2 * i + 1]), sc2, nm2);
-          const float2 t1 = __ffma2_rn(make_float2(s[c * 32 + 2 * i + 2], s[c * 32 + 2 * i + 3]), sc2, nm2);
-          const float2 e0 = make_float2(ex2(t0.x), ex2(t0.y)), e1 = make_float2(ex2(t1.x), ex2(t1.y));
-          l2a = __fadd2_rn(l2a, e0);
-          l2b = __fadd2_rn(l2b, e1);
-          pk[i] = pack2<BF16>(e0.x, e0.y);
-          pk[i + 1] = pack2<BF16>(e1.x, e1.y);
-        }
-        tmem_st16(s_tmem + c * 16, pk);
+      // The row maximum of the tile is known before the first exponential.  Taking it off the critical path
+      // (exponentials against the previous tiles' reference, rescale deferred by one tile) was measured on B200
+      // and changed nothing: 7.70-7.91 ms vs 7.60-7.80 ms at 32K (r02i) — the FMNMX3 chain already hides under the
+      // TMEM load latency.
+      {
+        const float m_new = fmaxf(m_ref, row_max());
+        const bool need = (j == 0) || (m_new > m_ref + p.rescale_threshold);
+        if (__any_sync(0xffffffffu, need)) rescale_to(m_new);
+        l += write_p();
       }
-      l += (l2a.x + l2b.x) + (l2a.y + l2b.y);
-#else
-      float l0 = 0.f, l1 = 0.f;
-#pragma unroll
-      for (int c = 0; c < kBN / 32; ++c) {
-        uint32_t pk[16];
-#pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          const float p0 = ex2(fmaf(s[c * 32 + 2 * i], p.scale_log2, neg_m));
-          const float p1 = ex2(fmaf(s[c * 32 + 2 * i + 1], p.scale_log2, neg_m));
-          l0 += p0;
-          l1 += p1;
-          pk[i] = pack2<BF16>(p0, p1);
-        }
-        tmem_st16(s_tmem + c * 16, pk);
-      }
-      l += l0 + l1;
-#endif
       tc_wait_st();
       tc_fence_before();
       mbar_arrive(&sm.p_full[t]);
