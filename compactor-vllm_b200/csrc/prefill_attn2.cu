@@ -143,6 +143,10 @@ prefill_attn2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
           row = q_beg + (j - n_pre) * kBN;
         }
         mbar_wait(&sm.empty[slot], ph ^ 1);
+#ifdef CVLLM_PROBE_NO_TMA  // timing probe only (wrong results): K / V tiles are never fetched
+        mbar_arrive(&sm.full[slot]);
+        continue;
+#endif
         mbar_expect_tx(&sm.full[slot], kTileBytes);
         unsigned char* dst = sm.kv[slot];
         if (pre) {
