@@ -42,6 +42,8 @@ _SIGNATURES = {
     "cvllm_ipc_free": (_i, [_p]),
     "cvllm_allreduce_oneshot": (_i, [_p, _i, _i, _p, _i64, _i, _p]),
     "cvllm_allreduce_twoshot": (_i, [_p, _i, _i, _p, _i64, _i, _i64, _p]),
+    "cvllm_gemm_allreduce_payload_bytes": (_i64, [_i64, _i64, _i]),
+    "cvllm_gemm_allreduce": (_i, [_p, _i64, _p, _i64, _i64, _i64, _i64, _p, _i, _i, _i, _i64, _p, _p]),
     "cvllm_rank_scores_workspace_bytes": (_sz, [_i, _i, _i]),
     "cvllm_rank_scores": (_i, [_p, _i64, _p, _i, _i, _i, _i, _p, _p, _sz, _p]),
     "cvllm_store_topk_workspace_bytes": (_sz, [_i, _i, _i, _i]),

@@ -126,6 +126,111 @@ class PeerAllReduce:
         self._own = None
 
 
+class PeerGemmAllReduce:
+    """`F.linear(x, W)` + `dist.all_reduce` of a row-parallel layer as ONE kernel per rank (csrc/gemm_reduce.cu,
+    `cvllm_gemm_allreduce`): tcgen05 GEMM on CTA pairs whose epilogue TMA-stores each tile into the owning rank's
+    memory over NVLink (reduce-scatter), reducer warps that sum a round of rows as soon as it has landed from every
+    rank and store the result into y on every rank (all-gather).  The route for PREFILL-size outputs, where the
+    separate all-reduce is 12-37 % of the layer.
+
+    `max_rows x out_features` sizes the shared buffer (slots + y, 2 x rows x out x 2 bytes per rank).  The returned
+    tensor is a view of that buffer, valid until the next call."""
+
+    def __init__(self, max_rows: int, out_features: int, group=None, device: Optional[torch.device] = None,
+                 _virtual: Optional[tuple] = None):
+        lib = N.lib()
+        self.device = device or torch.device("cuda", torch.cuda.current_device())
+        self.max_rows, self.out_features = int(max_rows), int(out_features)
+        self.flag_bytes = int(lib.cvllm_allreduce_flag_bytes())
+        if _virtual is not None:  # (rank, world, bases): several ranks of ONE process on one GPU (tests)
+            self.group = None
+            self.rank, self.world, bases = _virtual
+            self.capacity = int(lib.cvllm_gemm_allreduce_payload_bytes(self.max_rows, self.out_features, self.world))
+            self._own = None
+            self._bases = (C.c_void_p * self.world)(*bases)
+            return
+        assert dist.is_initialized(), "PeerGemmAllReduce needs an initialised process group"
+        self.group = group
+        self.rank = dist.get_rank(group)
+        self.world = dist.get_world_size(group)
+        assert self.world <= 8
+        self.capacity = int(lib.cvllm_gemm_allreduce_payload_bytes(self.max_rows, self.out_features, self.world))
+        assert self.capacity > 0
+        own = C.c_void_p()
+        handle = C.create_string_buffer(64)
+        with torch.cuda.device(self.device):
+            N.check(lib.cvllm_ipc_alloc(self.capacity, C.byref(own), handle), "cvllm_ipc_alloc")
+        handles = [None] * self.world
+        dist.all_gather_object(handles, bytes(handle.raw), group=group)
+        self._own = own.value
+        self._bases = (C.c_void_p * self.world)()
+        for r, h in enumerate(handles):
+            if r == self.rank:
+                self._bases[r] = self._own
+            else:
+                ptr = C.c_void_p()
+                with torch.cuda.device(self.device):
+                    N.check(lib.cvllm_ipc_open(C.create_string_buffer(h, 64), C.byref(ptr)), "cvllm_ipc_open")
+                self._bases[r] = ptr.value
+        dist.barrier(group=group)  # every rank has mapped every buffer before the first kernel
+
+    @staticmethod
+    def virtual_ranks(world: int, max_rows: int, out_features: int, device: torch.device):
+        """`world` ranks inside this process on ONE device (their kernels run side by side on `world` streams, each on
+        1/world of the SMs — set the `grs_pairs` test option accordingly).  Returns (ranks, free)."""
+        lib = N.lib()
+        cap = int(lib.cvllm_gemm_allreduce_payload_bytes(max_rows, out_features, world))
+        bases = []
+        with torch.cuda.device(device):
+            for _ in range(world):
+                own, handle = C.c_void_p(), C.create_string_buffer(64)
+                N.check(lib.cvllm_ipc_alloc(cap, C.byref(own), handle), "cvllm_ipc_alloc")
+                bases.append(own.value)
+        ranks = [PeerGemmAllReduce(max_rows, out_features, device=device, _virtual=(r, world, bases))
+                 for r in range(world)]
+
+        def free():
+            torch.cuda.synchronize(device)
+            for b in bases:
+                lib.cvllm_ipc_free(b)
+        return ranks, free
+
+    def supports(self, x: torch.Tensor, weight: torch.Tensor) -> bool:
+        rows = x.numel() // max(1, x.shape[-1])
+        return (x.is_cuda and x.dtype in (torch.bfloat16, torch.float16) and weight.dtype == x.dtype
+                and 0 < rows <= self.max_rows and weight.shape[0] == self.out_features
+                and weight.shape[0] % 8 == 0 and weight.shape[1] % 8 == 0 and weight.stride(1) == 1
+                and weight.stride(0) % 8 == 0)
+
+    def linear(self, x: torch.Tensor, weight: torch.Tensor) -> torch.Tensor:
+        """sum over ranks of `x @ weight.T` ([..., K_local] x [out, K_local]) -> [..., out], on every rank."""
+        rows = x.reshape(-1, x.shape[-1])
+        if rows.stride(1) != 1 or rows.stride(0) % 8 != 0:
+            rows = rows.contiguous()
+        m, k = rows.shape
+        n = weight.shape[0]
+        assert weight.shape[1] == k and self.supports(x, weight)
+        y_ptr = C.c_void_p()
+        rc = N.lib().cvllm_gemm_allreduce(N.ptr(rows), rows.stride(0), N.ptr(weight), weight.stride(0), m, n, k,
+                                          self._bases, self.rank, self.world, N.dtype_code(x.dtype), self.capacity,
+                                          C.byref(y_ptr), N.stream(self.device))
+        N.check(rc, "cvllm_gemm_allreduce")
+        raw = torch.as_tensor(_RawCudaBytes(y_ptr.value, m * n * 2), device=self.device)
+        return raw.view(x.dtype).view(*x.shape[:-1], n)
+
+    def close(self) -> None:
+        if self._own is None:
+            return
+        lib = N.lib()
+        torch.cuda.synchronize(self.device)
+        for r in range(self.world):
+            if r != self.rank and self._bases[r]:
+                lib.cvllm_ipc_close(self._bases[r])
+        dist.barrier(group=self.group)
+        lib.cvllm_ipc_free(self._own)
+        self._own = None
+
+
 def shard_rows(full_weight: torch.Tensor, rank: int, world: int) -> torch.Tensor:
     """Input-dimension shard of a [out, in] weight for tensor-parallel rank `rank` (reference :141-146)."""
     assert full_weight.shape[1] % world == 0
@@ -137,10 +242,12 @@ class RowParallelLinear(nn.Module):
     """y = all_reduce(x_shard @ W_shard^T (+ bias on rank 0)) — reference layers/linear.py:133-153."""
 
     def __init__(self, input_size: int, output_size: int, bias: bool = False,
-                 peer_all_reduce: Optional[PeerAllReduce] = None):
+                 peer_all_reduce: Optional[PeerAllReduce] = None,
+                 peer_gemm_all_reduce: Optional[PeerGemmAllReduce] = None):
         super().__init__()
         # the tensor-parallel group is the peer all-reduce's group when one is supplied (it may be a subgroup)
-        group = peer_all_reduce.group if peer_all_reduce is not None else None
+        group = peer_all_reduce.group if peer_all_reduce is not None else (
+            peer_gemm_all_reduce.group if peer_gemm_all_reduce is not None else None)
         self.tp_group = group
         self.tp_rank = dist.get_rank(group) if dist.is_initialized() else 0
         self.tp_size = dist.get_world_size(group) if dist.is_initialized() else 1
@@ -148,6 +255,7 @@ class RowParallelLinear(nn.Module):
         self.weight = nn.Parameter(torch.empty(output_size, input_size // self.tp_size))
         self.bias = nn.Parameter(torch.empty(output_size)) if bias else None
         self.peer = peer_all_reduce
+        self.peer_gemm = peer_gemm_all_reduce  # fused GEMM + reduce-scatter + all-gather for prefill-size outputs
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         bias = self.bias if self.tp_rank == 0 else None
@@ -162,6 +270,8 @@ class RowParallelLinear(nn.Module):
                 st = self.peer.staging((rows.shape[0], self.weight.shape[0]), x.dtype)
                 torch.mm(rows, self.weight.t(), out=st)  # the partial lands in the shared buffer: no copy
                 return self.peer.reduce_staged(st).view(out_shape)
+        if self.peer_gemm is not None and bias is None and self.bias is None and self.peer_gemm.supports(x, self.weight):
+            return self.peer_gemm.linear(x, self.weight)  # one kernel: GEMM, reduce-scatter and all-gather
         y = F.linear(x, self.weight, bias)
         dist.all_reduce(y, group=self.tp_group)
         return y

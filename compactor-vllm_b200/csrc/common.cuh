@@ -86,6 +86,8 @@ struct TestOptions {
   std::atomic<int> eig_trace{0};
   std::atomic<int> snap_v1{0};                // 1: the mma.sync SnapKV kernels
   std::atomic<int> chunk_scores_v1{0};        // 1: the mma.sync chunk scorer (A/B against the tcgen05 one)
+  std::atomic<int> grs_pairs{0};              // > 0: cap the CTA pairs of gemm_reduce (several virtual ranks on one GPU)
+  std::atomic<int> grs_rows_per_round{0};     // > 0: rows per reduce round of gemm_reduce (multiple of 256)
 };
 TestOptions& test_options();
 

@@ -165,6 +165,20 @@ int cvllm_allreduce_oneshot(void* const* peer_bases_host, int rank, int world, v
 int cvllm_allreduce_twoshot(void* const* peer_bases_host, int rank, int world, void* out,
                             int64_t numel, int dtype, int64_t result_offset_bytes, cvllm_stream_t stream);
 
+/* RowParallelLinear.forward as ONE kernel — layers/linear.py:133-153 (`F.linear` then `dist.all_reduce`), the o_proj of
+ * models/llama3.py:111.  y[M, N] = sum over ranks r of round16(x_r[M, K] . w_r[N, K]^T), fp32 sum in rank order,
+ * rounded once, identical bits on every rank.  The GEMM runs on tcgen05 CTA pairs; its epilogue TMA-stores each
+ * finished tile into the owning rank's buffer over NVLink (reduce-scatter), reducer warps of the same kernel sum a
+ * round of rows as soon as every rank's tiles for it have landed and store the result into y on every rank
+ * (all-gather).  Buffers: one cvllm_ipc_alloc(cvllm_gemm_allreduce_payload_bytes(M_max, N, world)) per rank, mapped
+ * by every rank (cvllm_ipc_open); a buffer is private to this entry (its flag words are not the all-reduce's).
+ * Every rank calls with the same M, N, dtype, in the same order.  *y_out_host = y inside peer_bases_host[rank]; it
+ * stays valid until the next call on this buffer.  Needs N, K, lda, ldw multiples of 8 (else CVLLM_E_UNSUPPORTED). */
+int64_t cvllm_gemm_allreduce_payload_bytes(int64_t M, int64_t N, int world);
+int cvllm_gemm_allreduce(const void* x, int64_t lda, const void* w, int64_t ldw, int64_t M, int64_t N, int64_t K,
+                         void* const* peer_bases_host, int rank, int world, int dtype,
+                         int64_t payload_capacity_bytes, void** y_out_host, cvllm_stream_t stream);
+
 /* ------------------------------------------------------------------------
  * Selection + compaction
  * --------------------------------------------------------------------- */
