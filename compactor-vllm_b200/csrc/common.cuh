@@ -87,6 +87,8 @@ struct TestOptions {
   std::atomic<int> snap_v1{0};                // 1: the mma.sync SnapKV kernels
   std::atomic<int> chunk_scores_v1{0};        // 1: the mma.sync chunk scorer (A/B against the tcgen05 one)
   std::atomic<int> grs_pairs{0};              // > 0: cap the CTA pairs of gemm_reduce (several virtual ranks on one GPU)
+  std::atomic<int> grs_probe{0};              // gemm_reduce timing probes (bit mask; results are wrong)
+  std::atomic<uint64_t> grs_debug_host_ptr{0};  // pinned host buffer for gemm_reduce's timeout records
   std::atomic<int> grs_rows_per_round{0};     // > 0: rows per reduce round of gemm_reduce (multiple of 256)
 };
 TestOptions& test_options();

@@ -12,7 +12,7 @@
 //     memory unless the owner is this rank), then adds 1 to a counter in the owner's memory (system-scope release).
 //     Ranks walk the owners in rotated order (rank+1, rank+2, ...), so at any time every NVLink port has one sender
 //     and one receiver, and the transfer of tile i overlaps the math of tile i+1;
-//   * owner blocks are cut into ROUNDS of R rows.  Four reducer warps per CTA wait until every rank's counter for a
+//   * owner blocks are cut into ROUNDS of R rows.  Eight reducer warps per CTA wait until every rank's counter for a
 //     round is complete, sum the `world` slots in rank order in fp32, and store the 16-bit result into y on EVERY rank
 //     (the all-gather, also by peer stores) — while the tensor pipe is already working on later rounds;
 //   * a call ends when every peer has signalled that all its stores into this rank's y are performed.
@@ -40,14 +40,14 @@ constexpr int kABytes = kBM * kBK * 2;         // 16 KB: x rows of this CTA
 constexpr int kBBytes = (kBN / 2) * kBK * 2;   // 16 KB: this CTA's half of the W tile
 constexpr int kStageBytes = kABytes + kBBytes;
 constexpr int kBoxBytes = 128 * 128;           // [128 rows x 64 cols] 16-bit, 128-byte swizzled rows
-constexpr int kThreads = 384;                  // warps: 0 TMA, 1 UMMA, 2 forwarder, 3 TMEM, 4-7 epilogue, 8-11 reducer
+constexpr int kThreads = 512;                  // warps: 0 TMA, 1 UMMA, 3 TMEM, 4-7 epilogue, 8-15 reducer
+constexpr int kReducers = 256;
 constexpr int kMaxWorld = 8;
 constexpr int kMaxRounds = 128;
 // flag words at the start of a rank's buffer (the kArFlagBytes header of cvllm_ipc_alloc, zeroed at allocation)
 constexpr int kWEpoch = 0, kWFin = 1, kWStarted = 8, kWDone = 16, kWCnt = 32;  // kWCnt + round * 8 + source rank
 constexpr size_t kHeaderBytes = 6656;  // == cvllm_allreduce_flag_bytes()
 static_assert((kWCnt + kMaxRounds * 8) * 4 <= kHeaderBytes, "flag words fit the header");
-constexpr uint32_t kSpinLimit = 1u << 26;
 }  // namespace grs
 
 struct alignas(64) GrsMaps {
@@ -61,12 +61,14 @@ struct GrsParams {
   int Mo, R, C;                // rows per owner, rows per round, rounds (Mo = C * R)
   int NT, KS, mc;              // column tiles, k steps, pair tiles (256 rows) per round
   int rank, world, n_pairs;
+  uint32_t* dbg;               // pinned host words for the timeout records (test option), or null
+  int probe;                   // timing probes (test option grs_probe; wrong results): 1 no TMA loads, 2 no UMMA, 4 no stores, 8 no reduce
 };
 
 struct __align__(1024) GrsSmem {
   uint8_t ab[grs::kStages][grs::kStageBytes];
   uint8_t out[2][grs::kBoxBytes];
-  uint64_t full[grs::kStages], empty[grs::kStages], pair_full[grs::kStages];
+  uint64_t full[grs::kStages], empty[grs::kStages];  // full: the LEADER's counts both CTAs' bytes
   uint64_t acc_full[2], acc_empty[2];
   uint32_t tmem_base, epoch;
 };
@@ -80,12 +82,60 @@ __device__ __forceinline__ uint32_t grs_ld_flag(const uint32_t* p) {
   return v;
 }
 __device__ __forceinline__ void grs_fence_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
-// spin on a word of THIS rank's memory until it reaches `want` (peers write it); bounded: a missing peer traps
-__device__ __forceinline__ void grs_wait_ge(const uint32_t* p, uint32_t want) {
+// Every wait of this kernel is bounded by TIME (%globaltimer; 4 s for a pair's own barriers, 20 s for flags other ranks write): a protocol bug or a missing peer ends in a trap,
+// not a hung GPU.  With the `grs_debug_host_ptr` test option (a pinned host buffer, 8 words per CTA) the first words say
+// which wait gave up: {code, thread, a, b, observed}; codes 1 producer/empty, 2 issuer/acc_empty, 3 issuer/full,
+// 4 epilogue/acc_full, 5 STARTED, 6 round counter, 7 DONE.
+__device__ __forceinline__ uint64_t grs_now() {
+  uint64_t t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __noinline__ void grs_fail(uint32_t* dbg, uint32_t code, uint32_t a, uint32_t b, uint32_t seen) {
+  if (dbg) {
+    volatile uint32_t* d = dbg + 8 * blockIdx.x;
+    d[1] = threadIdx.x; d[2] = a; d[3] = b; d[4] = seen; d[0] = code;
+    __threadfence_system();
+    __nanosleep(2000000);  // let the other stuck waits of the grid write their records before the trap kills it
+  }
+  __trap();
+}
+constexpr uint64_t kGrsTimeoutNs = 4000000000ull;        // shared-memory barriers: this CTA pair only
+constexpr uint64_t kGrsPeerTimeoutNs = 20000000000ull;   // flags written by other ranks (launch skew included)
+__device__ __forceinline__ void grs_mbar_wait(uint64_t* bar, uint32_t parity, uint32_t* dbg, uint32_t code, uint32_t a,
+                                              uint32_t b) {
+  if (mbar_try_wait(bar, parity)) return;
+  const uint64_t t0 = grs_now();
   uint32_t spins = 0;
-  while ((int32_t)(grs_ld_flag(p) - want) < 0) {
+  while (!mbar_try_wait(bar, parity))
+    if ((++spins & 1023) == 0 && grs_now() - t0 > kGrsTimeoutNs) grs_fail(dbg, code, a, b, 0);
+}
+__device__ __forceinline__ void grs_mbar_wait_cluster(uint64_t* bar, uint32_t parity, uint32_t* dbg, uint32_t code,
+                                                      uint32_t a, uint32_t b) {
+  const uint64_t t0 = grs_now();
+  uint32_t spins = 0;
+  for (;;) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    if (ok) return;
+    if ((++spins & 1023) == 0 && grs_now() - t0 > kGrsTimeoutNs) grs_fail(dbg, code, a, b, 0);
+  }
+}
+// spin on a word of THIS rank's memory until it reaches `want` (peers write it)
+__device__ __forceinline__ void grs_wait_ge(const uint32_t* p, uint32_t want, uint32_t* dbg, uint32_t code, uint32_t a) {
+  uint32_t seen = grs_ld_flag(p);
+  if ((int32_t)(seen - want) >= 0) return;
+  const uint64_t t0 = grs_now();
+  uint32_t spins = 0;
+  while ((int32_t)((seen = grs_ld_flag(p)) - want) < 0) {
     __nanosleep(100);
-    if (++spins > grs::kSpinLimit) __trap();
+    if ((++spins & 255) == 0 && grs_now() - t0 > kGrsPeerTimeoutNs) grs_fail(dbg, code, a, want, seen);
   }
 }
 __device__ __forceinline__ uint4 grs_ld_v4(const void* p) {
@@ -114,6 +164,46 @@ __device__ __forceinline__ GrsTile grs_decode(const GrsParams& p, int j) {
   return t;
 }
 
+// Vectors [lo, hi) of my owner block (16-byte units): sum the W slots in rank order, store to y on every rank.
+// U vectors per thread per trip with all U x W loads issued before the first use (W x U = 8 loads in flight).
+template <bool BF16, int W, int U>
+__device__ __forceinline__ void grs_reduce_span(const GrsParams& p, const char* slots, int64_t slot_stride,
+                                                int64_t y_row0, int64_t lo, int64_t hi, int rt) {
+  const int64_t stride = (int64_t)gridDim.x * grs::kReducers;
+  for (int64_t i0 = lo + (int64_t)blockIdx.x * grs::kReducers + rt; i0 < hi; i0 += stride * U) {
+    uint4 v[U][W];
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+#pragma unroll
+      for (int r = 0; r < W; ++r)
+        if (r < p.world && i0 + u * stride < hi) v[u][r] = grs_ld_v4(slots + r * slot_stride + (i0 + u * stride) * 16);
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int64_t i = i0 + u * stride;
+      if (i >= hi) break;
+      float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int r = 0; r < W; ++r) {
+        if (r < p.world) {  // rank order on every rank: identical bits everywhere
+          const uint32_t w[4] = {v[u][r].x, v[u][r].y, v[u][r].z, v[u][r].w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const float2 f = unpack2<BF16>(w[e]);
+            acc[2 * e] += f.x;
+            acc[2 * e + 1] += f.y;
+          }
+        }
+      }
+      uint4 o;
+      o.x = pack2<BF16>(acc[0], acc[1]); o.y = pack2<BF16>(acc[2], acc[3]);
+      o.z = pack2<BF16>(acc[4], acc[5]); o.w = pack2<BF16>(acc[6], acc[7]);
+#pragma unroll
+      for (int r = 0; r < W; ++r)
+        if (r < p.world) reinterpret_cast<uint4*>(reinterpret_cast<char*>(p.base[r]) + p.y_off)[y_row0 + i] = o;
+    }
+  }
+}
+
 template <bool BF16>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(grs::kThreads, 1)
 gemm_reduce_kernel(const __grid_constant__ GrsMaps maps, const GrsParams p) {
@@ -129,7 +219,6 @@ gemm_reduce_kernel(const __grid_constant__ GrsMaps maps, const GrsParams p) {
     for (int s = 0; s < kStages; ++s) {
       mbar_init(&sm.full[s], 1);
       mbar_init(&sm.empty[s], 1);
-      mbar_init(&sm.pair_full[s], 2);
     }
     for (int t = 0; t < 2; ++t) {
       mbar_init(&sm.acc_full[t], 1);
@@ -153,6 +242,9 @@ gemm_reduce_kernel(const __grid_constant__ GrsMaps maps, const GrsParams p) {
 
   if (warp == 0) {
     // ===================== TMA producer: my 128 rows of x, my half of the W tile =====================
+    // The bytes of BOTH CTAs are counted on the leader's `full` barrier (cp.async.bulk.tensor.cta_group::2): the
+    // issuer's single wait covers the pair's four boxes; a forwarding hop through a warp of each CTA cost a
+    // release.cluster arrive per stage (~540 clk, serialised: as long as the stage's four UMMAs).
     if (lane == 0) {
       int n_it = 0;
       for (int j = pair; j < jobs; j += p.n_pairs) {
@@ -160,24 +252,15 @@ gemm_reduce_kernel(const __grid_constant__ GrsMaps maps, const GrsParams p) {
         if (t.m_pair0 >= p.M) continue;
         for (int ks = 0; ks < p.KS; ++ks, ++n_it) {
           const int s = n_it % kStages;
-          mbar_wait(&sm.empty[s], ((n_it / kStages) & 1) ^ 1);
-          mbar_expect_tx(&sm.full[s], kStageBytes);
-          tma_load_2d(sm.ab[s], &maps.a, &sm.full[s], ks * kBK, t.m_pair0 + kBM * (int)cr);
-          tma_load_2d(sm.ab[s] + kABytes, &maps.b, &sm.full[s], ks * kBK, t.n0 + (kBN / 2) * (int)cr);
-        }
-      }
-    }
-  } else if (warp == 2) {
-    // ===================== forwarder: my stage landed -> the leader's pair barrier =====================
-    if (lane == 0) {
-      int n_it = 0;
-      for (int j = pair; j < jobs; j += p.n_pairs) {
-        const GrsTile t = grs_decode(p, j);
-        if (t.m_pair0 >= p.M) continue;
-        for (int ks = 0; ks < p.KS; ++ks, ++n_it) {
-          const int s = n_it % kStages;
-          mbar_wait(&sm.full[s], (n_it / kStages) & 1);
-          mbar_arrive_cluster(&sm.pair_full[s], 0);
+          grs_mbar_wait(&sm.empty[s], ((n_it / kStages) & 1) ^ 1, p.dbg, 1, n_it, j);
+          if (p.probe & 1) {
+            if (cr == 0) mbar_arrive(&sm.full[s]);
+            continue;
+          }
+          if (cr == 0) mbar_expect_tx(&sm.full[s], 2 * kStageBytes);
+          const uint32_t bar = mapa_u32(&sm.full[s], 0);
+          tma_load_2d_pair(sm.ab[s], &maps.a, bar, ks * kBK, t.m_pair0 + kBM * (int)cr);
+          tma_load_2d_pair(sm.ab[s] + kABytes, &maps.b, bar, ks * kBK, t.n0 + (kBN / 2) * (int)cr);
         }
       }
     }
@@ -190,14 +273,15 @@ gemm_reduce_kernel(const __grid_constant__ GrsMaps maps, const GrsParams p) {
         const GrsTile t = grs_decode(p, j);
         if (t.m_pair0 >= p.M) continue;
         const int buf = t_it & 1;
-        mbar_wait_cluster(&sm.acc_empty[buf], ((t_it >> 1) & 1) ^ 1);
+        grs_mbar_wait_cluster(&sm.acc_empty[buf], ((t_it >> 1) & 1) ^ 1, p.dbg, 2, t_it, j);
         tc_fence_after();
         const uint32_t d_tmem = tmem + buf * kBN;
         for (int ks = 0; ks < p.KS; ++ks, ++n_it) {
           const int s = n_it % kStages;
-          mbar_wait_cluster(&sm.pair_full[s], (n_it / kStages) & 1);
+          grs_mbar_wait(&sm.full[s], (n_it / kStages) & 1, p.dbg, 3, n_it, j);
           tc_fence_after();
           const uint32_t a_addr = smem_u32(sm.ab[s]), b_addr = a_addr + kABytes;
+          if (!(p.probe & 2))
 #pragma unroll
           for (int kk = 0; kk < kBK / 16; ++kk)
             umma2_ss(d_tmem, umma_smem_desc(a_addr + kk * 32, 16, 1024), umma_smem_desc(b_addr + kk * 32, 16, 1024),
@@ -220,10 +304,10 @@ gemm_reduce_kernel(const __grid_constant__ GrsMaps maps, const GrsParams p) {
       const GrsTile t = grs_decode(p, j);
       if (t.m_pair0 >= p.M) continue;
       const int buf = t_it & 1;
-      mbar_wait(&sm.acc_full[buf], (t_it >> 1) & 1);
+      grs_mbar_wait(&sm.acc_full[buf], (t_it >> 1) & 1, p.dbg, 4, t_it, j);
       tc_fence_after();
       const int m0 = t.m_pair0 + kBM * (int)cr;
-      const bool valid = m0 < p.M;  // the upper CTA of the last pair tile may hold only padding rows
+      const bool valid = m0 < p.M && !(p.probe & 4);  // the upper CTA of the last pair tile may hold only padding rows
       const int dest_row = p.rank * p.Mo + (m0 - t.owner * p.Mo);
 #pragma unroll 1
       for (int ch = 0; ch < 4; ++ch) {
@@ -290,8 +374,8 @@ gemm_reduce_kernel(const __grid_constant__ GrsMaps maps, const GrsParams p) {
       grs_fence_sys();
       grs_st_flag(reinterpret_cast<uint32_t*>(p.base[rt]) + kWStarted + p.rank, epoch);
     }
-    if (rt < p.world) grs_wait_ge(flags + kWStarted + rt, epoch);
-    asm volatile("bar.sync 2, 128;" ::: "memory");
+    if (rt < p.world) grs_wait_ge(flags + kWStarted + rt, epoch, p.dbg, 5, rt);
+    asm volatile("bar.sync 2, 256;" ::: "memory");
     const int my_rows = max(0, min(p.M - p.rank * p.Mo, p.Mo));
     const int64_t row_vecs = p.N / 8;
     const char* slots = reinterpret_cast<const char*>(p.base[p.rank]) + p.slot_off;
@@ -299,40 +383,17 @@ gemm_reduce_kernel(const __grid_constant__ GrsMaps maps, const GrsParams p) {
     const int64_t y_row0 = (int64_t)p.rank * p.Mo * row_vecs;
     for (int c = 0; c < p.C; ++c) {
       const int r_lo = c * p.R;
-      if (r_lo >= my_rows) break;
+      if (r_lo >= my_rows || (p.probe & 12)) break;
       const int r_hi = min(r_lo + p.R, my_rows);
       const uint32_t expected = (uint32_t)((r_hi - r_lo + kBM - 1) / kBM) * (uint32_t)p.NT;
-      if (rt < p.world) grs_wait_ge(flags + kWCnt + c * 8 + rt, expected);
-      asm volatile("bar.sync 2, 128;" ::: "memory");
+      if (rt < p.world) grs_wait_ge(flags + kWCnt + c * 8 + rt, expected, p.dbg, 6, c);
+      asm volatile("bar.sync 2, 256;" ::: "memory");
       const int64_t lo = r_lo * row_vecs, hi = r_hi * row_vecs;
-      for (int64_t i = lo + (int64_t)blockIdx.x * 128 + rt; i < hi; i += (int64_t)gridDim.x * 128) {
-        uint4 v[kMaxWorld];
-#pragma unroll
-        for (int r = 0; r < kMaxWorld; ++r)
-          if (r < p.world) v[r] = grs_ld_v4(slots + r * slot_stride + i * 16);
-        float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-        for (int r = 0; r < kMaxWorld; ++r) {
-          if (r < p.world) {
-            const uint32_t w[4] = {v[r].x, v[r].y, v[r].z, v[r].w};
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              const float2 f = unpack2<BF16>(w[e]);
-              acc[2 * e] += f.x;
-              acc[2 * e + 1] += f.y;
-            }
-          }
-        }
-        uint4 o;
-        o.x = pack2<BF16>(acc[0], acc[1]); o.y = pack2<BF16>(acc[2], acc[3]);
-        o.z = pack2<BF16>(acc[4], acc[5]); o.w = pack2<BF16>(acc[6], acc[7]);
-#pragma unroll
-        for (int r = 0; r < kMaxWorld; ++r)
-          if (r < p.world)
-            reinterpret_cast<uint4*>(reinterpret_cast<char*>(p.base[r]) + p.y_off)[y_row0 + i] = o;
-      }
+      if (p.world <= 2) grs_reduce_span<BF16, 2, 4>(p, slots, slot_stride, y_row0, lo, hi, rt);
+      else if (p.world <= 4) grs_reduce_span<BF16, 4, 2>(p, slots, slot_stride, y_row0, lo, hi, rt);
+      else grs_reduce_span<BF16, 8, 1>(p, slots, slot_stride, y_row0, lo, hi, rt);
     }
-    asm volatile("bar.sync 2, 128;" ::: "memory");
+    asm volatile("bar.sync 2, 256;" ::: "memory");
     if (rt == 0) {
       grs_fence_sys();
       uint32_t old;
@@ -346,7 +407,7 @@ gemm_reduce_kernel(const __grid_constant__ GrsMaps maps, const GrsParams p) {
           grs_st_flag(reinterpret_cast<uint32_t*>(p.base[r]) + kWDone + p.rank, epoch);
       }
     }
-    if (rt < p.world) grs_wait_ge(flags + kWDone + rt, epoch);  // every peer's stores into my y are performed
+    if (rt < p.world) grs_wait_ge(flags + kWDone + rt, epoch, p.dbg, 7, rt);  // every peer's stores into my y are performed
   }
 
   tc_fence_before();
@@ -413,6 +474,8 @@ extern "C" int cvllm_gemm_allreduce(const void* x, int64_t lda, const void* w, i
   const int cap = test_options().grs_pairs.load();
   if (cap > 0 && cap < pairs) pairs = cap;
   p.n_pairs = pairs;
+  p.probe = test_options().grs_probe.load();
+  p.dbg = reinterpret_cast<uint32_t*>(static_cast<uintptr_t>(test_options().grs_debug_host_ptr.load()));
 
   GrsMaps maps;
   const bool bf16 = dtype == CVLLM_BF16;

@@ -266,6 +266,22 @@ __device__ __forceinline__ void umma2_commit(uint64_t* bar) {
       "h"((unsigned short)3)
       : "memory");
 }
+// address of `p` (a location in my shared memory) as seen in CTA `rank` of the cluster
+__device__ __forceinline__ uint32_t mapa_u32(const void* p, uint32_t rank) {
+  uint32_t remote;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(smem_u32(p)), "r"(rank));
+  return remote;
+}
+// TMA load of a CTA pair: the box lands in MY shared memory, the bytes are counted on `bar_cluster_addr`, a barrier
+// of either CTA of the pair (the leader's: one wait covers both CTAs' halves, no forwarding hop)
+__device__ __forceinline__ void tma_load_2d_pair(void* dst, const CUtensorMap* m, uint32_t bar_cluster_addr, int c0,
+                                                 int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], "
+      "[%2];" ::"r"(smem_u32(dst)),
+      "l"(reinterpret_cast<uint64_t>(m)), "r"(bar_cluster_addr), "r"(c0), "r"(c1)
+      : "memory");
+}
 // shared memory (SW128 box) -> global through a tensor map; completion is tracked by bulk async-groups
 __device__ __forceinline__ void tma_store_2d(const CUtensorMap* m, const void* src, int c0, int c1) {
   asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
