@@ -494,20 +494,23 @@ def cfg5_block(dev, rank: int, world: int, ranks, steps: int) -> dict:
     and the tensor-parallel all-reduce (layers/linear.py:149-153: NCCL for the 512 MiB prefill message, the
     peer-memory kernel for the B=16 decode step).  STRONG scaling: the layer is fixed, ranks split it."""
     import torch.distributed as dist
-    from compactor_vllm.layers.linear import PeerAllReduce, RowParallelLinear
+    from compactor_vllm.layers.linear import PeerAllReduce, PeerGemmAllReduce, RowParallelLinear
     hq, hkv, hidden, n_tok = 64 // world, 8 // world, 8192, SEQ
     mx = ranks.max
     res = {"tp": world, "hq_local": hq, "hkv_local": hkv, "hidden": hidden, "tokens": n_tok, "scaling": "strong"}
     w = Workload(dev, n_tok, seed=555 + rank, hq=hq, hkv=hkv)
     res["retain_local"] = w.retain
     peer = PeerAllReduce() if world > 1 else None
-    lin = RowParallelLinear(hidden, hidden, peer_all_reduce=peer).to(dev).to(torch.bfloat16)
+    # prefill-size o_proj: ONE kernel does the GEMM, the reduce-scatter and the all-gather over NVLink peer memory
+    # (csrc/gemm_reduce.cu); the cuBLAS GEMM + NCCL all-reduce route is timed beside it
+    fused = PeerGemmAllReduce(n_tok, hidden) if world > 1 else None
+    lin = RowParallelLinear(hidden, hidden, peer_all_reduce=peer, peer_gemm_all_reduce=fused).to(dev).to(torch.bfloat16)
     with torch.no_grad():
         lin.weight.normal_(0.0, 0.02)
 
         y = torch.empty((n_tok, hidden), dtype=torch.bfloat16, device=dev)  # o_proj output, reused every step
 
-        def prefill():
+        def prefill_lib():
             ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
             ev[0].record()
             out = w.prefill_step()
@@ -519,22 +522,52 @@ def cfg5_block(dev, rank: int, world: int, ranks, steps: int) -> dict:
             ev[3].record()
             return ev
 
+        def prefill_fused():
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+            ev[0].record()
+            out = w.prefill_step()
+            ev[1].record()
+            yf = lin(out.reshape(n_tok, hq * D))  # RowParallelLinear -> cvllm_gemm_allreduce
+            ev[2].record()
+            return ev, yf
+
+        n_rep = max(3, steps // 4)
         for _ in range(3):
-            prefill()
+            prefill_lib()
         ranks.barrier()
-        evs = [prefill() for _ in range(max(3, steps // 4))]
+        evs = [prefill_lib() for _ in range(n_rep)]
         torch.cuda.synchronize()
-        mean = lambda i, j: sum(e[i].elapsed_time(e[j]) for e in evs) / len(evs)  # noqa: E731
-        res["per_rank_ms"] = [round(mean(0, 1), 3), round(mean(1, 2), 3), round(mean(2, 3), 3)]  # rank 0's own
-        res["prefill_ms"] = mx(mean(0, 3))
-        res["attn_compress_ms"] = mx(mean(0, 1))
-        res["oproj_gemm_ms"] = mx(mean(1, 2))
-        res["allreduce_ms"] = mx(mean(2, 3)) if world > 1 else 0.0
-        res["allreduce_share"] = res["allreduce_ms"] / res["prefill_ms"]
+        mean = lambda es, i, j: sum(e[i].elapsed_time(e[j]) for e in es) / len(es)  # noqa: E731
+        res["per_rank_ms"] = [round(mean(evs, 0, 1), 3), round(mean(evs, 1, 2), 3), round(mean(evs, 2, 3), 3)]
+        res["attn_compress_ms"] = mx(mean(evs, 0, 1))
+        res["oproj_gemm_ms"] = mx(mean(evs, 1, 2))
+        res["allreduce_ms"] = mx(mean(evs, 2, 3)) if world > 1 else 0.0
+        lib_ms = mx(mean(evs, 0, 3))
+        res["prefill_ms_cublas_nccl"] = lib_ms
         msg = n_tok * hidden * 2
         res["allreduce_bytes"] = msg
         if world > 1:
             res["allreduce_busbw_gbs"] = 2 * (world - 1) / world * msg / (res["allreduce_ms"] * 1e-3) / 1e9
+            for _ in range(3):
+                prefill_fused()
+            ranks.barrier()
+            fevs = [prefill_fused() for _ in range(n_rep)]
+            torch.cuda.synchronize()
+            only = [e for e, _ in fevs]
+            res["oproj_fused_ms"] = mx(mean(only, 1, 2))
+            res["prefill_ms"] = mx(mean(only, 0, 2))
+            res["oproj_route"] = "fused tcgen05 GEMM + reduce-scatter + all-gather over peer memory (one kernel)"
+            res["oproj_fused_speedup"] = (res["oproj_gemm_ms"] + res["allreduce_ms"]) / res["oproj_fused_ms"]
+            # same sum as the library route: NCCL's order may differ in the last bit of a few entries
+            prefill_lib()
+            _, yf = prefill_fused()
+            torch.cuda.synchronize()
+            res["oproj_fused_max_abs_diff_vs_nccl"] = ranks.max(float((yf.float() - y.float()).abs().max()))
+            res["oproj_fused_frac_equal_nccl"] = 1.0 - ranks.max(float((yf != y).float().mean()))
+        else:
+            res["prefill_ms"] = lib_ms
+            res["oproj_route"] = "cuBLAS (tp = 1: no collective)"
+        res["allreduce_share"] = res["allreduce_ms"] / lib_ms
         res["prefill_tflops"] = prefill_flops(n_tok, hq=64) / (res["prefill_ms"] * 1e-3) / 1e12
         kept = w.cache.bh_seq_lens[0, w.slot].cpu()
         res["kept_pairs_local"] = int(kept.sum())
@@ -559,6 +592,7 @@ def cfg5_block(dev, rank: int, world: int, ranks, steps: int) -> dict:
             res["allreduce_checks_ok"] = bool(ranks.sum(0.0 if chk["ok"] else 1.0) == 0)
             res["allreduce_checks"] = chk["checks"]
             peer.close()
+            fused.close()
     del w, lin
     torch.cuda.empty_cache()
     return res

@@ -62,7 +62,7 @@ struct GrsParams {
   int NT, KS, mc;              // column tiles, k steps, pair tiles (256 rows) per round
   int rank, world, n_pairs;
   uint32_t* dbg;               // pinned host words for the timeout records (test option), or null
-  int probe;                   // timing probes (test option grs_probe; wrong results): 1 no TMA loads, 2 no UMMA, 4 no stores, 8 no reduce
+  int probe;                   // timing probes (test option grs_probe; wrong results): 1 no TMA loads, 2 no UMMA, 4 no stores, 8 no reduce, 16 no L2 hints
 };
 
 struct __align__(1024) GrsSmem {
@@ -83,8 +83,8 @@ __device__ __forceinline__ uint32_t grs_ld_flag(const uint32_t* p) {
 }
 __device__ __forceinline__ void grs_fence_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
 // Every wait of this kernel is bounded by TIME (%globaltimer; 4 s for a pair's own barriers, 20 s for flags other ranks write): a protocol bug or a missing peer ends in a trap,
-// not a hung GPU.  With the `grs_debug_host_ptr` test option (a pinned host buffer, 8 words per CTA) the first words say
-// which wait gave up: {code, thread, a, b, observed}; codes 1 producer/empty, 2 issuer/acc_empty, 3 issuer/full,
+// not a hung GPU.  With the `grs_debug_host_ptr` test option (a pinned host buffer, 64 words per CTA) each wait that
+// gave up leaves {code, thread, a, b, observed} at word 8 * code; codes 1 producer/empty, 2 issuer/acc_empty, 3 issuer/full,
 // 4 epilogue/acc_full, 5 STARTED, 6 round counter, 7 DONE.
 __device__ __forceinline__ uint64_t grs_now() {
   uint64_t t;
@@ -93,10 +93,12 @@ __device__ __forceinline__ uint64_t grs_now() {
 }
 __device__ __noinline__ void grs_fail(uint32_t* dbg, uint32_t code, uint32_t a, uint32_t b, uint32_t seen) {
   if (dbg) {
-    volatile uint32_t* d = dbg + 8 * blockIdx.x;
+    volatile uint32_t* d = dbg + 64 * blockIdx.x + 8 * code;
     d[1] = threadIdx.x; d[2] = a; d[3] = b; d[4] = seen; d[0] = code;
     __threadfence_system();
-    __nanosleep(2000000);  // let the other stuck waits of the grid write their records before the trap kills it
+    // let the other stuck waits of the grid write their records before the trap kills it
+    const uint64_t t0 = grs_now();
+    while (grs_now() - t0 < 200000000ull) __nanosleep(1000000);
   }
   __trap();
 }
@@ -108,7 +110,7 @@ __device__ __forceinline__ void grs_mbar_wait(uint64_t* bar, uint32_t parity, ui
   const uint64_t t0 = grs_now();
   uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity))
-    if ((++spins & 1023) == 0 && grs_now() - t0 > kGrsTimeoutNs) grs_fail(dbg, code, a, b, 0);
+    if ((++spins & 15) == 0 && grs_now() - t0 > kGrsTimeoutNs) grs_fail(dbg, code, a, b, 0);
 }
 __device__ __forceinline__ void grs_mbar_wait_cluster(uint64_t* bar, uint32_t parity, uint32_t* dbg, uint32_t code,
                                                       uint32_t a, uint32_t b) {
@@ -124,7 +126,7 @@ __device__ __forceinline__ void grs_mbar_wait_cluster(uint64_t* bar, uint32_t pa
         : "r"(smem_u32(bar)), "r"(parity)
         : "memory");
     if (ok) return;
-    if ((++spins & 1023) == 0 && grs_now() - t0 > kGrsTimeoutNs) grs_fail(dbg, code, a, b, 0);
+    if ((++spins & 15) == 0 && grs_now() - t0 > kGrsTimeoutNs) grs_fail(dbg, code, a, b, 0);
   }
 }
 // spin on a word of THIS rank's memory until it reaches `want` (peers write it)
@@ -138,10 +140,21 @@ __device__ __forceinline__ void grs_wait_ge(const uint32_t* p, uint32_t want, ui
     if ((++spins & 255) == 0 && grs_now() - t0 > kGrsPeerTimeoutNs) grs_fail(dbg, code, a, want, seen);
   }
 }
+// A slot line is written once per call (by a TMA store, maybe a peer's) and read once, after the acquire on its
+// round's counter (ordered by that acquire and the reducers' barrier): streaming policy, so that the GEMM's operands
+// stay in L2, not the slots.
 __device__ __forceinline__ uint4 grs_ld_v4(const void* p) {
   uint4 r;
-  asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  asm volatile("ld.global.cs.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p)
+               : "memory");
   return r;
+}
+__device__ __forceinline__ void grs_st_v4(void* p, const uint4& v) {
+  asm volatile("st.global.cs.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x),
+               "r"(v.y), "r"(v.z), "r"(v.w)
+               : "memory");
 }
 
 // job j of this rank -> pair tile.  Order: round c, then owner (rank+1, rank+2, ..., rank), then the round's pair
@@ -199,7 +212,7 @@ __device__ __forceinline__ void grs_reduce_span(const GrsParams& p, const char* 
       o.z = pack2<BF16>(acc[4], acc[5]); o.w = pack2<BF16>(acc[6], acc[7]);
 #pragma unroll
       for (int r = 0; r < W; ++r)
-        if (r < p.world) reinterpret_cast<uint4*>(reinterpret_cast<char*>(p.base[r]) + p.y_off)[y_row0 + i] = o;
+        if (r < p.world) grs_st_v4(reinterpret_cast<uint4*>(reinterpret_cast<char*>(p.base[r]) + p.y_off) + y_row0 + i, o);
     }
   }
 }
@@ -245,7 +258,9 @@ gemm_reduce_kernel(const __grid_constant__ GrsMaps maps, const GrsParams p) {
     // The bytes of BOTH CTAs are counted on the leader's `full` barrier (cp.async.bulk.tensor.cta_group::2): the
     // issuer's single wait covers the pair's four boxes; a forwarding hop through a warp of each CTA cost a
     // release.cluster arrive per stage (~540 clk, serialised: as long as the stage's four UMMAs).
-    if (lane == 0) {
+    if (lane == 0 && !((p.probe & 1) && cr != 0)) {
+      const uint64_t pol_a = (p.probe & 16) ? kL2EvictNormal : kL2EvictFirst;
+      const uint64_t pol_b = (p.probe & 16) ? kL2EvictNormal : kL2EvictLast;
       int n_it = 0;
       for (int j = pair; j < jobs; j += p.n_pairs) {
         const GrsTile t = grs_decode(p, j);
@@ -253,14 +268,15 @@ gemm_reduce_kernel(const __grid_constant__ GrsMaps maps, const GrsParams p) {
         for (int ks = 0; ks < p.KS; ++ks, ++n_it) {
           const int s = n_it % kStages;
           grs_mbar_wait(&sm.empty[s], ((n_it / kStages) & 1) ^ 1, p.dbg, 1, n_it, j);
-          if (p.probe & 1) {
-            if (cr == 0) mbar_arrive(&sm.full[s]);
+          if (p.probe & 1) {  // the leader free-runs; its peer is not part of the handshake and must not follow it
+            mbar_arrive(&sm.full[s]);  // (a follower that falls a lap behind misses a phase flip and waits for ever)
             continue;
           }
           if (cr == 0) mbar_expect_tx(&sm.full[s], 2 * kStageBytes);
           const uint32_t bar = mapa_u32(&sm.full[s], 0);
-          tma_load_2d_pair(sm.ab[s], &maps.a, bar, ks * kBK, t.m_pair0 + kBM * (int)cr);
-          tma_load_2d_pair(sm.ab[s] + kABytes, &maps.b, bar, ks * kBK, t.n0 + (kBN / 2) * (int)cr);
+          // x rows are used by one sweep over the column tiles and never again; W is re-read by every row tile
+          tma_load_2d_pair_hint(sm.ab[s], &maps.a, bar, ks * kBK, t.m_pair0 + kBM * (int)cr, pol_a);
+          tma_load_2d_pair_hint(sm.ab[s] + kABytes, &maps.b, bar, ks * kBK, t.n0 + (kBN / 2) * (int)cr, pol_b);
         }
       }
     }

@@ -6,10 +6,17 @@ On ONE GPU the whole protocol runs with several VIRTUAL ranks: `world` buffers i
 rotated owner order, reducer rounds and peer stores are exactly those of `world` GPUs; only the wires differ).
 Bars: (1) world == 1 against a torch fp32 GEMM within bf16 rounding; (2) world > 1 BIT-EXACT against the fp32
 rank-order sum, rounded once, of each rank's own world == 1 output (the all-reduce's contract, csrc/allreduce.cu)."""
+import json
+import socket
+import subprocess
+import sys
+from pathlib import Path
+
 import pytest
 import torch
 
 pytestmark = pytest.mark.gpu
+ROOT = Path(__file__).resolve().parent.parent
 
 
 def _option(name, value):
@@ -124,3 +131,22 @@ def test_refuses_unaligned_shapes(options):
             ranks[0].linear(x, w)
     finally:
         free()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs (NVLink peer memory between processes)")
+@pytest.mark.parametrize("rows", [4096, 1000])
+def test_two_processes_two_gpus(rows):
+    """One process per GPU, buffers shared by cudaIpc handles: every rank holds the same bits, and they are the fp32
+    rank-order sum of the ranks' own cuBLAS partials (tools/gemm_reduce_bench.py does the checks on the devices)."""
+    with socket.socket() as sk:
+        sk.bind(("127.0.0.1", 0))
+        port = sk.getsockname()[1]
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+           "127.0.0.1", "--master-port", str(port), str(ROOT / "tools" / "gemm_reduce_bench.py"), str(rows)]
+    run = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert run.returncode == 0, run.stderr[-2000:]
+    line = [ln for ln in run.stdout.splitlines() if ln.startswith("{")][-1]
+    res = json.loads(line)
+    assert res["identical_on_all_ranks"] is True
+    assert res["frac_equal_rank_order_sum_of_cublas_partials"] == 1.0
+    assert res["max_abs_diff_vs_nccl"] <= res["max_abs"] * 2.0 ** -7

@@ -90,7 +90,7 @@ def multi_gpu(dev, rank, world, m=32768, n=8192, hidden=8192):
     dist.all_gather(all_d, digest)
     same = all(bool(torch.equal(d, all_d[0])) for d in all_d)
     # exact contract: fp32 rank-order sum of the ranks' own rounded partials (gathered on rank 0 for a slice of rows)
-    rows = 512
+    rows = min(512, m)
     part = torch.mm(x[:rows], w.t())
     parts = [torch.zeros_like(part) for _ in range(world)]
     dist.all_gather(parts, part)
@@ -128,7 +128,8 @@ def main():
         return
     import torch.distributed as dist
     dist.init_process_group("nccl", device_id=dev)
-    res = multi_gpu(dev, rank, world)
+    m = int(sys.argv[1]) if len(sys.argv) > 1 else 32768
+    res = multi_gpu(dev, rank, world, m=m)
     if rank == 0:
         print(json.dumps(res))
     dist.destroy_process_group()

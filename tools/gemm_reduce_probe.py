@@ -1,5 +1,5 @@
 """Where the time of csrc/gemm_reduce.cu goes on ONE GPU (world 1): timing probes through the `grs_probe` test option
-(1 no TMA loads, 2 no UMMA, 4 no epilogue stores / reduce, 8 no reduce).  Probe results are wrong by construction."""
+(1 no TMA loads, 2 no UMMA, 4 no epilogue stores / reduce, 8 no reduce, 16 no L2 hints).  Probe results are wrong by construction."""
 import json
 import sys
 from pathlib import Path
@@ -34,17 +34,18 @@ DBG = None
 
 
 def report_failure():
-    rec = DBG.view(-1, 8)
-    bad = (rec[:, 0] != 0).nonzero().flatten().tolist()
-    print("timeout records (cta: code thread a b seen):", file=sys.stderr)
-    for i in bad[:40]:
-        print("  ", i, rec[i, :5].tolist(), file=sys.stderr)
+    rec = DBG.view(-1, 8, 8)
+    print("timeout records (cta: [code thread a b seen] ...):", file=sys.stderr)
+    for cta in range(rec.shape[0]):
+        rows = [rec[cta, c, :5].tolist() for c in range(8) if int(rec[cta, c, 0]) != 0]
+        if rows:
+            print("  ", cta, rows, file=sys.stderr)
 
 
 def main():
     global DBG
     dev = torch.device("cuda", 0)
-    DBG = torch.zeros(8 * 160, dtype=torch.int32).pin_memory()
+    DBG = torch.zeros(64 * 160, dtype=torch.int32).pin_memory()
     opt("grs_debug_host_ptr", DBG.data_ptr())
     m, n = 32768, 8192
     out = []
@@ -56,11 +57,12 @@ def main():
             x = torch.randn((m, k), device=dev).to(torch.bfloat16)
             w = torch.randn((n, k), device=dev).to(torch.bfloat16)
             row = {"k": k, "rows_per_round": rpr or 256}
-            for name, probe in (("full", 0), ("no_reduce", 8), ("gemm_only", 4), ("no_tma", 5), ("no_mma", 6),
-                                ("skeleton", 7)):
+            for name, probe in (("full", 0), ("full_nohint", 16), ("no_reduce", 8), ("gemm_only", 4),
+                                ("gemm_only_nohint", 20), ("no_tma", 5), ("no_mma", 6), ("skeleton", 7)):
                 opt("grs_probe", probe)
+                print("probe start", k, name, file=sys.stderr, flush=True)
                 row[name + "_ms"] = round(timed(lambda: pg.linear(x, w)), 4)
-                print("   ", k, name, row[name + "_ms"], file=sys.stderr, flush=True)
+                print("probe", k, name, row[name + "_ms"], file=sys.stderr, flush=True)
             opt("grs_probe", 0)
             row["gemm_only_tflops"] = round(2.0 * m * n * k / row["gemm_only_ms"] / 1e9, 1)
             out.append(row)
