@@ -46,6 +46,8 @@ _SIGNATURES = {
     "cvllm_gemm_allreduce": (_i, [_p, _i64, _p, _i64, _i64, _i64, _i64, _p, _i, _i, _i, _i64, _p, _p]),
     "cvllm_rank_scores_workspace_bytes": (_sz, [_i, _i, _i]),
     "cvllm_rank_scores": (_i, [_p, _i64, _p, _i, _i, _i, _i, _p, _p, _sz, _p]),
+    "cvllm_rank_scores_static_max_bytes": (_sz, []),
+    "cvllm_rank_scores_static": (_i, [_p, _i64, _p, _i, _i, _i, _i, _p, _p]),
     "cvllm_store_topk_workspace_bytes": (_sz, [_i, _i, _i, _i]),
     "cvllm_prefill_store_topk_idx": (_i, [_p, _p, _i64, _i64, _i64, _i64, _p, _i, _i, _p, _p, _p,
                                           _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _i, _i, _i,

@@ -419,6 +419,63 @@ extern "C" int cvllm_rank_scores(const float* scores, int64_t s_stride_n, const 
   return CVLLM_OK;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// cvllm_rank_scores_static: the same ranking with NO caller workspace and no allocation anywhere.  Added
+// for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops,
+// harnesses that forbid it); it has no counterpart in the reference.  The scratch of the radix sort (two key / index
+// ping-pong buffers + the per-tile histograms) lives in a file-scope device array of kRankStaticBytes = 8 MiB, which
+// every GPU that loads the library holds until exit.  8 MiB covers B x max_k_len x H <= ~510 K scores (e.g. one
+// 32768-token sequence x 8 KV heads = 4.1 MiB, or 16 sequences x 4096 tokens x 8 heads); larger problems are
+// refused with CVLLM_E_UNSUPPORTED and must use cvllm_rank_scores with their own workspace.
+// Every word of the scratch that a call reads it has written first (sort_init fills keys0 / idx0, sort_hist writes
+// every histogram cell), so nothing needs clearing between calls.  ALL calls on a device share the one array: two calls
+// that overlap on the GPU (different streams, or graphs replayed concurrently) race; calls on one stream are ordered.
+// In HOST code `g_rank_static` is only the symbol's host-side stand-in, never a device address: the address is taken
+// once per device with cudaGetSymbolAddress (with that device current) and that pointer is what the kernels get.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr size_t kRankStaticBytes = (size_t)8 << 20;
+static __device__ __align__(256) unsigned char g_rank_static[kRankStaticBytes];
+
+static int rank_static_scratch(void** out) {
+  constexpr int kMaxDev = 64;
+  static std::atomic<void*> cached[kMaxDev];
+  int dev = 0;
+  CVLLM_CHECK_CUDA(cudaGetDevice(&dev));
+  CVLLM_CHECK_ARG(dev >= 0 && dev < kMaxDev);
+  void* p = cached[dev].load(std::memory_order_acquire);
+  if (!p) {
+    CVLLM_CHECK_CUDA(cudaGetSymbolAddress(&p, g_rank_static));  // this device's copy of the array
+    CVLLM_CHECK_ARG(p != nullptr && (reinterpret_cast<uintptr_t>(p) & 255) == 0);
+    cached[dev].store(p, std::memory_order_release);
+  }
+  *out = p;
+  return CVLLM_OK;
+}
+
+extern "C" size_t cvllm_rank_scores_static_max_bytes(void) { return kRankStaticBytes; }
+
+extern "C" int cvllm_rank_scores_static(const float* scores, int64_t s_stride_n, const int32_t* cu_seqlens_k, int B,
+                                        int H, int max_k_len, int top_k, int64_t* out_indices,
+                                        cvllm_stream_t stream) {
+  CVLLM_CHECK_ARG(B > 0 && H > 0 && max_k_len >= 0 && top_k >= 0);
+  if ((int64_t)max_k_len * H == 0 || top_k == 0) return CVLLM_OK;
+  const size_t need = cvllm_rank_scores_workspace_bytes(B, H, max_k_len);
+  if (need > kRankStaticBytes) {
+    char msg[200];
+    snprintf(msg, sizeof(msg),
+             "cvllm_rank_scores_static: B=%d x max_k_len=%d x H=%d needs %zu bytes of scratch, the built-in array "
+             "holds %zu; use cvllm_rank_scores with a caller workspace",
+             B, max_k_len, H, need, kRankStaticBytes);
+    set_last_error(msg);
+    return CVLLM_E_UNSUPPORTED;
+  }
+  void* scratch = nullptr;
+  const int rc = rank_static_scratch(&scratch);
+  if (rc != CVLLM_OK) return rc;
+  return cvllm_rank_scores(scores, s_stride_n, cu_seqlens_k, B, H, max_k_len, top_k, out_indices, scratch,
+                           kRankStaticBytes, stream);
+}
+
 template <int V>
 static void launch_gather(const void* keys, const void* vals, int64_t sk_n, int64_t sk_h, int64_t sv_n,
                           int64_t sv_h, const int32_t* pos, const int32_t* cu, const int32_t* bm,

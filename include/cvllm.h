@@ -194,6 +194,18 @@ int cvllm_rank_scores(const float* scores, int64_t s_stride_n,
                       const int32_t* cu_seqlens_k, int B, int H, int max_k_len,
                       int top_k, int64_t* out_indices, void* workspace,
                       size_t workspace_bytes, cvllm_stream_t stream);
+/* The same ranking with NO caller workspace and no allocation of any kind (no cudaMalloc / cudaFree / allocating
+ * library call).  No counterpart in the reference: added for callers that cannot
+ * allocate (CUDA-graph capture, tight serving loops, harnesses that forbid cudaMalloc).  The sort's scratch is a
+ * file-scope device array of cvllm_rank_scores_static_max_bytes() = 8 MiB that every GPU loading the library holds
+ * until exit; problems whose cvllm_rank_scores_workspace_bytes(B, H, max_k_len) exceeds it (more than ~510 K scores)
+ * return CVLLM_E_UNSUPPORTED with the sizes in cvllm_last_error().  All calls on a device SHARE the array: calls that
+ * overlap on the GPU (different streams) race; nothing needs clearing between calls.  Output identical to
+ * cvllm_rank_scores. */
+size_t cvllm_rank_scores_static_max_bytes(void);
+int cvllm_rank_scores_static(const float* scores, int64_t s_stride_n,
+                             const int32_t* cu_seqlens_k, int B, int H, int max_k_len,
+                             int top_k, int64_t* out_indices, cvllm_stream_t stream);
 
 /* prefill_store_topk_kv — kv_cache/store_kv_cache.py:9-248 (K4 + K5), index
  * flavour: `indices` is the [B, max_sel] ranking (int32 or int64 by
