@@ -62,6 +62,16 @@ struct Prefill2Smem {
   uint32_t tmem_base;
 };
 
+#ifdef CVLLM_PREFILL_TRACE  // profiling build only (tools/trace_prefill.py): clock64 stamps of CTA (0,0,0), first 256 KV tiles
+__device__ long long g_p2_trace[8][256];
+#define P2_TRACE(rowi, jj)                                                                              \
+  do {                                                                                                  \
+    if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && lane == 0 && (jj) < 256) g_p2_trace[rowi][jj] = clock64(); \
+  } while (0)
+#else
+#define P2_TRACE(rowi, jj) do { } while (0)
+#endif
+
 template <bool BF16>
 __global__ void __launch_bounds__(p2::kThreads, 1)
 prefill_attn2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
@@ -189,6 +199,7 @@ prefill_attn2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
     // O_t += P_t . V_j  (V_j in ring entry 2j + 1, already waited for)
     auto issue_pv = [&](int t, int j) {
       mbar_wait(&sm.p_full[t], j & 1);
+      P2_TRACE(2 * t, j);
       tc_fence_after();
       if (lane == 0) {
         const uint32_t v_addr = smem_u32(sm.kv[slot_of(2 * j + 1)]);
@@ -241,8 +252,10 @@ prefill_attn2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
         wait_k(j + 1);
         issue_qk(0, j + 1);
       }
+      P2_TRACE(1, j);
       issue_pv(1, j);
       if (more) issue_qk(1, j + 1);
+      P2_TRACE(3, j);
     }
   } else if (warp < 8) {
     // ====================== softmax / correction / epilogue ======================
@@ -258,10 +271,12 @@ prefill_attn2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
 
     for (int j = 0; j < n_tiles; ++j) {
       mbar_wait(&sm.s_full[t], j & 1);
+      if (quad == 0) P2_TRACE(4 + 2 * t, j);
       tc_fence_after();
 #ifdef CVLLM_PROBE_NO_SOFTMAX  // timing probe only (wrong results): the issuer / TMA side alone — 6.4 ms at 32K
       tc_fence_before();
       mbar_arrive(&sm.p_full[t]);
+      if (quad == 0) P2_TRACE(5 + 2 * t, j);
       continue;
 #endif
       float s[kBN];
@@ -360,6 +375,7 @@ prefill_attn2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
       tc_wait_st();
       tc_fence_before();
       mbar_arrive(&sm.p_full[t]);
+      if (quad == 0) P2_TRACE(5 + 2 * t, j);
     }
 
     // ---- epilogue: O / l -> out ----
@@ -426,3 +442,12 @@ int cvllm_launch_prefill2(const CUtensorMap& tm_q, const CUtensorMap& tm_k, cons
   CVLLM_CHECK_LAUNCH();
   return CVLLM_OK;
 }
+
+#ifdef CVLLM_PREFILL_TRACE
+// profiling build only: copies the 8 x 256 clock64 stamps of the last launch's CTA (0,0,0) to host memory
+extern "C" int cvllm_debug_prefill_trace_read(void* host_out) {
+  CVLLM_CHECK_CUDA(cudaDeviceSynchronize());
+  CVLLM_CHECK_CUDA(cudaMemcpyFromSymbol(host_out, cvllm::g_p2_trace, sizeof(long long) * 8 * 256));
+  return CVLLM_OK;
+}
+#endif
