@@ -179,17 +179,26 @@ prefill_attn2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
     auto slot_of = [](int n) { return n % kSlots; };
     auto phase_of = [](int n) { return (uint32_t)((n / kSlots) & 1); };
 
+    // The issuing thread is on the critical path of every hand-off (tools/trace_prefill.py: 86 cycles per UMMA in the
+    // loop against 64 on the pipe, 13 SASS instructions each).  Two things keep its per-UMMA work to a few uniform-
+    // datapath instructions: the TMEM base is made provably warp-uniform (a shuffle from lane 0: otherwise every UMMA
+    // is wrapped in an ELECT / R2UR / branch loop), and a descriptor is its tile's base descriptor plus a constant
+    // (the 14-bit start-address field cannot carry: shared memory ends below 256 KB) instead of a shift and two masks.
+    const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem, 0);
+    auto desc_at = [](uint64_t base, uint32_t byte_off) {
+      return (base & 0xffffffff00000000ull) | (uint64_t)((uint32_t)base + (byte_off >> 4));
+    };
+    const uint64_t q_desc[2] = {umma_smem_desc(smem_u32(sm.q[0]), 16, 1024), umma_smem_desc(smem_u32(sm.q[1]), 16, 1024)};
+
     // S_t = Q_t . K_j^T  (K_j in ring entry 2j, already waited for)
     auto issue_qk = [&](int t, int j) {
       if (lane == 0) {
-        const uint32_t q_addr = smem_u32(sm.q[t]);
-        const uint32_t k_addr = smem_u32(sm.kv[slot_of(2 * j)]);
-        const uint32_t s_tmem = tmem + t * kBN;
+        const uint64_t k_desc = umma_smem_desc(smem_u32(sm.kv[slot_of(2 * j)]), 16, 1024);
+        const uint32_t s_tmem = tmem_u + t * kBN;
 #pragma unroll
         for (int kk = 0; kk < kHD / 16; ++kk) {
           const uint32_t off = (kk >> 2) * kBoxBytes + (kk & 3) * 32;
-          umma_ss(s_tmem, umma_smem_desc(q_addr + off, 16, 1024), umma_smem_desc(k_addr + off, 16, 1024),
-                  idesc_qk, kk > 0 ? 1u : 0u);
+          umma_ss(s_tmem, desc_at(q_desc[t], off), desc_at(k_desc, off), idesc_qk, kk > 0 ? 1u : 0u);
         }
         umma_commit(&sm.s_full[t]);
         if (t == 1) umma_commit(&sm.empty[slot_of(2 * j)]);  // K_j consumed by both heads
@@ -202,14 +211,12 @@ prefill_attn2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
       P2_TRACE(2 * t, j);
       tc_fence_after();
       if (lane == 0) {
-        const uint32_t v_addr = smem_u32(sm.kv[slot_of(2 * j + 1)]);
-        const uint32_t p_tmem = tmem + t * kBN;
-        const uint32_t o_tmem = tmem + 256 + t * kHD;
+        const uint64_t v_desc = umma_smem_desc(smem_u32(sm.kv[slot_of(2 * j + 1)]), kBoxBytes, 1024);
+        const uint32_t p_tmem = tmem_u + t * kBN;
+        const uint32_t o_tmem = tmem_u + 256 + t * kHD;
 #pragma unroll
-        for (int kk = 0; kk < kBN / 16; ++kk) {
-          const uint64_t vdesc = umma_smem_desc(v_addr + kk * 2048, kBoxBytes, 1024);
-          umma_ts(o_tmem, p_tmem + kk * 8, vdesc, idesc_pv, (j > 0 || kk > 0) ? 1u : 0u);
-        }
+        for (int kk = 0; kk < kBN / 16; ++kk)
+          umma_ts(o_tmem, p_tmem + kk * 8, desc_at(v_desc, kk * 2048), idesc_pv, (j > 0 || kk > 0) ? 1u : 0u);
         if (t == 1) umma_commit(&sm.empty[slot_of(2 * j + 1)]);  // V_j consumed by both heads
         umma_commit(&sm.o_done[t]);
         if (j == n_tiles - 1) umma_commit(&sm.o_final[t]);
