@@ -282,8 +282,16 @@ gemm_reduce_kernel(const __grid_constant__ GrsMaps maps, const GrsParams p) {
     }
   } else if (warp == 1) {
     // ===================== UMMA issuer (leader CTA only) =====================
-    if (cr == 0 && lane == 0) {
+    // The whole warp walks the schedule (every value below is warp-uniform: kernel parameters, blockIdx, loop counters,
+    // the TMEM base shuffled from lane 0) and lane 0 only executes the tcgen05 instructions: the compiler then keeps
+    // addresses and descriptors on the uniform datapath.  Computed inside a one-lane region they live in vector
+    // registers and every UMMA is preceded by five R2UR moves inside an ELECT loop (21 SASS instructions per UMMA; the
+    // same finding as the prefill issuer, tools/trace_prefill.py).  A descriptor is its stage's base descriptor plus a
+    // constant (the 14-bit start-address field cannot carry: shared memory ends below 256 KB).
+    if (cr == 0) {
       constexpr uint32_t idesc = umma_idesc(BF16, 2 * kBM, kBN, false, false);
+      const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem, 0);
+      const uint32_t ab0 = smem_u32(sm.ab[0]);
       int n_it = 0, t_it = 0;
       for (int j = pair; j < jobs; j += p.n_pairs) {
         const GrsTile t = grs_decode(p, j);
@@ -291,20 +299,26 @@ gemm_reduce_kernel(const __grid_constant__ GrsMaps maps, const GrsParams p) {
         const int buf = t_it & 1;
         grs_mbar_wait_cluster(&sm.acc_empty[buf], ((t_it >> 1) & 1) ^ 1, p.dbg, 2, t_it, j);
         tc_fence_after();
-        const uint32_t d_tmem = tmem + buf * kBN;
+        const uint32_t d_tmem = tmem_u + buf * kBN;
         for (int ks = 0; ks < p.KS; ++ks, ++n_it) {
           const int s = n_it % kStages;
           grs_mbar_wait(&sm.full[s], (n_it / kStages) & 1, p.dbg, 3, n_it, j);
           tc_fence_after();
-          const uint32_t a_addr = smem_u32(sm.ab[s]), b_addr = a_addr + kABytes;
-          if (!(p.probe & 2))
+          if (lane == 0) {
+            const uint64_t a_desc = umma_smem_desc(ab0 + s * kStageBytes, 16, 1024);
+            const uint64_t hi = a_desc & 0xffffffff00000000ull;
+            const uint32_t a_lo = (uint32_t)a_desc, b_lo = a_lo + (kABytes >> 4);
+            if (!(p.probe & 2))
 #pragma unroll
-          for (int kk = 0; kk < kBK / 16; ++kk)
-            umma2_ss(d_tmem, umma_smem_desc(a_addr + kk * 32, 16, 1024), umma_smem_desc(b_addr + kk * 32, 16, 1024),
-                     idesc, (ks > 0 || kk > 0) ? 1u : 0u);
-          umma2_commit(&sm.empty[s]);  // both CTAs' stage s may be refilled
+            for (int kk = 0; kk < kBK / 16; ++kk)
+              umma2_ss(d_tmem, hi | (uint64_t)(a_lo + 2 * kk), hi | (uint64_t)(b_lo + 2 * kk), idesc,
+                       (ks > 0 || kk > 0) ? 1u : 0u);
+            umma2_commit(&sm.empty[s]);  // both CTAs' stage s may be refilled
+          }
+          __syncwarp();
         }
-        umma2_commit(&sm.acc_full[buf]);
+        if (lane == 0) umma2_commit(&sm.acc_full[buf]);
+        __syncwarp();
         ++t_it;
       }
     }

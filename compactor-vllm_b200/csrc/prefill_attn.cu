@@ -159,7 +159,9 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_const
     // ============================ UMMA issuer ============================
     constexpr uint32_t idesc_qk = umma_idesc(BF16, kBM, kBN, false, false);
     constexpr uint32_t idesc_pv = umma_idesc(BF16, kBM, kHD, false, true);
-    const uint32_t q_addr = smem_u32(sm.q);
+    const uint64_t q_desc = umma_smem_desc(smem_u32(sm.q), 16, 1024);
+    // warp-uniform copies for the issuing thread (no R2UR loop per UMMA; see prefill_attn2.cu)
+    const uint32_t tmem_s0u = __shfl_sync(0xffffffffu, tmem_s0, 0), tmem_ou = tmem_s0u + 256;
 
     auto issue_pv = [&](int i) {
       const int sb = i & 1, st = i % kStages;
@@ -180,13 +182,11 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_const
       }
       tc_fence_after();
       if (lane == 0) {
-        const uint32_t v_addr = smem_u32(sm.v[st]);
-        const uint32_t p_tmem = tmem_s0 + sb * kBN;
+        const uint64_t v_desc = umma_smem_desc(smem_u32(sm.v[st]), kBoxBytes, 1024);
+        const uint32_t p_tmem = tmem_s0u + sb * kBN;
 #pragma unroll
-        for (int kk = 0; kk < kBN / 16; ++kk) {
-          const uint64_t vdesc = umma_smem_desc(v_addr + kk * 2048, kBoxBytes, 1024);
-          umma_ts(tmem_o, p_tmem + kk * 8, vdesc, idesc_pv, (i > 0 || kk > 0) ? 1u : 0u);
-        }
+        for (int kk = 0; kk < kBN / 16; ++kk)
+          umma_ts(tmem_ou, p_tmem + kk * 8, umma_desc_add(v_desc, kk * 2048), idesc_pv, (i > 0 || kk > 0) ? 1u : 0u);
         umma_commit(&sm.v_empty[st]);
         umma_commit(&sm.o_done);
         if (i == n_tiles - 1) umma_commit(&sm.o_final);
@@ -200,13 +200,12 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_const
       mbar_wait(&sm.k_full[st], (j / kStages) & 1);
       tc_fence_after();
       if (lane == 0) {
-        const uint32_t k_addr = smem_u32(sm.k[st]);
-        const uint32_t s_tmem = tmem_s0 + (j & 1) * kBN;
+        const uint64_t k_desc = umma_smem_desc(smem_u32(sm.k[st]), 16, 1024);
+        const uint32_t s_tmem = tmem_s0u + (j & 1) * kBN;
 #pragma unroll
         for (int kk = 0; kk < kHD / 16; ++kk) {
           const uint32_t off = (kk >> 2) * kBoxBytes + (kk & 3) * 32;
-          umma_ss(s_tmem, umma_smem_desc(q_addr + off, 16, 1024), umma_smem_desc(k_addr + off, 16, 1024),
-                  idesc_qk, kk > 0 ? 1u : 0u);
+          umma_ss(s_tmem, umma_desc_add(q_desc, off), umma_desc_add(k_desc, off), idesc_qk, kk > 0 ? 1u : 0u);
         }
         umma_commit(&sm.k_empty[st]);
         umma_commit(&sm.s_full[j & 1]);

@@ -144,6 +144,7 @@ chunk_scores_umma_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
     // ============================ UMMA issuer ============================
     asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsOther));
     constexpr uint32_t idesc = umma_idesc(BF16, kTile, kTile, false, false);
+    const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem, 0);  // warp-uniform for the compiler: no R2UR per UMMA
     int it = 0, qn = 0;  // qn doubles as the CTA-local tile counter: TMEM buffer qn % 4
     for (int idx = next_valid(blockIdx.x); idx < total; idx = next_valid(idx + gridDim.x), ++it) {
       const int kb = it % kKBufs;
@@ -155,13 +156,13 @@ chunk_scores_umma_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
         mbar_wait(&sm.s_empty[buf], ((qn >> 2) & 1) ^ 1);
         tc_fence_after();
         if (lane == 0) {
-          const uint32_t q_addr = smem_u32(qring0 + (size_t)slot * kTileBytes);
-          const uint32_t k_addr = smem_u32(kbuf0 + (size_t)kb * kTileBytes);
+          const uint64_t q_desc = umma_smem_desc(smem_u32(qring0 + (size_t)slot * kTileBytes), 16, 1024);
+          const uint64_t k_desc = umma_smem_desc(smem_u32(kbuf0 + (size_t)kb * kTileBytes), 16, 1024);
 #pragma unroll
           for (int kk = 0; kk < kHD / 16; ++kk) {
             const uint32_t off = (kk >> 2) * kBoxBytes + (kk & 3) * 32;
-            umma_ss(tmem + buf * kTile, umma_smem_desc(q_addr + off, 16, 1024),
-                    umma_smem_desc(k_addr + off, 16, 1024), idesc, kk > 0 ? 1u : 0u);
+            umma_ss(tmem_u + buf * kTile, umma_desc_add(q_desc, off), umma_desc_add(k_desc, off), idesc,
+                    kk > 0 ? 1u : 0u);
           }
           umma_commit(&sm.s_full[buf]);
           umma_commit(&sm.q_empty[slot]);

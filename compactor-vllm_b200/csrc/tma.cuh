@@ -201,6 +201,12 @@ __device__ __forceinline__ uint64_t umma_smem_desc(uint32_t smem_addr, uint32_t 
   d |= (uint64_t)2 << 61;
   return d;
 }
+// The descriptor of the same operand `byte_off` bytes further: base + constant.  The 14-bit start-address field cannot
+// carry (shared memory ends below 256 KB), so the issuing thread spends one uniform add per descriptor instead of a
+// shift and two masks — it is on the critical path of every hand-off (tools/trace_prefill.py).
+__device__ __forceinline__ uint64_t umma_desc_add(uint64_t base, uint32_t byte_off) {
+  return (base & 0xffffffff00000000ull) | (uint64_t)((uint32_t)base + (byte_off >> 4));
+}
 // Instruction descriptor (32-bit) for kind::f16, fp32 accumulate:
 //   [4,6) c fmt (1=f32)  [7,10) a fmt  [10,13) b fmt (0=f16, 1=bf16)
 //   [15] a major  [16] b major (0=K, 1=MN)  [17,23) N>>3  [24,29) M>>4
