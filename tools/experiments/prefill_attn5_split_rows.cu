@@ -66,6 +66,7 @@ struct Prefill2Smem {
   uint32_t tmem_base;
   int xmax[2][128];  // per (head, row): running row maximum as an order-preserving int (atomicMax by the row's two threads)
 };
+static_assert(sizeof(Prefill2Smem) + 1024 <= 232448, "shared memory of one CTA (227 KB)");
 
 #ifndef CVLLM_PREFILL_POLY_EVERY
 #define CVLLM_PREFILL_POLY_EVERY 0
@@ -236,7 +237,8 @@ prefill_attn2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
         const uint32_t o_tmem = tmem_u + 256 + t * kHD;
 #pragma unroll
         for (int kk = 0; kk < kBN / 16; ++kk)
-          umma_ts(o_tmem, p_tmem + kk * 8, desc_at(v_desc, kk * 2048), idesc_pv, (j > 0 || kk > 0) ? 1u : 0u);
+          umma_ts(o_tmem, p_tmem + kk * 8 + (kk >= kBN / 32 ? 32 : 0), desc_at(v_desc, kk * 2048), idesc_pv,
+                  (j > 0 || kk > 0) ? 1u : 0u);  // P of keys 0..63 at columns [0, 32), of keys 64..127 at [64, 96)
         if (t == 1) umma_commit(&sm.empty[slot_of(2 * j + 1)]);  // V_j consumed by both heads
         umma_commit(&sm.o_done[t]);
         if (j == n_tiles - 1) umma_commit(&sm.o_final[t]);
@@ -314,46 +316,51 @@ prefill_attn2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
       if (quad == 0 && half == 0) P2_TRACE(5 + 2 * t, j);
       continue;
 #endif
-      float s[kHalf];
+      // ---- pass 1: both 32-column pieces of my half, row maximum ----
+      // X = columns [c0, c0 + 32), Y = [c0 + 32, c0 + 64).  X stays in registers; Y is needed again after the
+      // exponentials of X and is simply read again from TMEM: 64 live logits + the packing registers do not fit the
+      // 96 registers that 18 warps leave each thread, and a second tcgen05.ld costs far less than spills in the loop.
+      uint32_t x[32];
+      auto mask = [&](uint32_t (&a)[32], int col_base) {  // boundary tiles only
+        if (j < n_pre) {
+          const int valid = Lc - j * kBN - col_base;
+          if (valid < 32) {
 #pragma unroll
-      for (int c = 0; c < kHalf / 32; ++c) {
-        uint32_t tmp[32];
-        tmem_ld32(s_tmem + c0 + c * 32, tmp);
+            for (int c = 0; c < 32; ++c)
+              if (c >= valid) a[c] = 0xff800000u;  // -inf
+          }
+        } else if (j == n_tiles - 1) {
 #pragma unroll
-        for (int i = 0; i < 32; ++i) s[c * 32 + i] = __uint_as_float(tmp[i]);
-      }
-      tc_wait_ld();
-
-      // ---- masks (boundary tiles only) ----
-      if (j < n_pre) {
-        const int valid = Lc - j * kBN - c0;
-        if (valid < kHalf) {
-#pragma unroll
-          for (int c = 0; c < kHalf; ++c)
-            if (c >= valid) s[c] = -INFINITY;
+          for (int c = 0; c < 32; ++c)
+            if (col_base + c > row) a[c] = 0xff800000u;
         }
-      } else if (j == n_tiles - 1) {
-#pragma unroll
-        for (int c = 0; c < kHalf; ++c)
-          if (c0 + c > row) s[c] = -INFINITY;
-      }
-
-      // ---- running row maximum over both halves ----
+      };
       {
-        float mx0 = s[0], mx1 = s[1], mx2 = s[2], mx3 = s[3];
+        uint32_t y[32];
+        tmem_ld32(s_tmem + c0 + 32, y);
+        tmem_ld32(s_tmem + c0, x);
+        tc_wait_ld();
+        mask(y, c0 + 32);
+        mask(x, c0);
+        float mx0 = __uint_as_float(x[0]), mx1 = __uint_as_float(x[1]), mx2 = __uint_as_float(x[2]),
+              mx3 = __uint_as_float(x[3]);
 #pragma unroll
-        for (int c = 4; c < kHalf; c += 4) {
-          mx0 = fmaxf(mx0, s[c]);
-          mx1 = fmaxf(mx1, s[c + 1]);
-          mx2 = fmaxf(mx2, s[c + 2]);
-          mx3 = fmaxf(mx3, s[c + 3]);
+        for (int c = 4; c < 32; c += 4) {
+          mx0 = fmaxf(mx0, __uint_as_float(x[c]));
+          mx1 = fmaxf(mx1, __uint_as_float(x[c + 1]));
+          mx2 = fmaxf(mx2, __uint_as_float(x[c + 2]));
+          mx3 = fmaxf(mx3, __uint_as_float(x[c + 3]));
+        }
+#pragma unroll
+        for (int c = 0; c < 32; c += 4) {
+          mx0 = fmaxf(mx0, __uint_as_float(y[c]));
+          mx1 = fmaxf(mx1, __uint_as_float(y[c + 1]));
+          mx2 = fmaxf(mx2, __uint_as_float(y[c + 2]));
+          mx3 = fmaxf(mx3, __uint_as_float(y[c + 3]));
         }
         atomicMax(xm, enc(fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3)) * p.scale_log2));
       }
-      // After this barrier (a) both threads of a row see the same running maximum, hence take the same rescale
-      // decisions, and (b) the partner has finished READING its S columns: P of keys 64..127 is written over
-      // S columns 32..63, which belong to the other half.
-      pair_sync();
+      pair_sync();  // both threads of a row now see the same running maximum, hence take the same rescale decisions
       const float m_run = dec(*reinterpret_cast<volatile int*>(xm));  // max over every tile so far, both halves
 
       // O *= alpha, l *= alpha, m_ref <- m_to.  O holds PV(0..j-1); PV(j-1) may still be in flight.  Each thread of
@@ -366,45 +373,44 @@ prefill_attn2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
           mbar_wait(&sm.o_done[t], (j - 1) & 1);
           tc_fence_after();
 #pragma unroll
-          for (int c = 0; c < kHalf / 32; ++c) {
-            uint32_t o[32];
-            tmem_ld32(o_tmem + c * 32, o);
+          for (int c = 0; c < kHalf / 16; ++c) {
+            uint32_t o[16];
+            tmem_ld16(o_tmem + c * 16, o);
             tc_wait_ld();
 #pragma unroll
-            for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
-            tmem_st32(o_tmem + c * 32, o);
+            for (int i = 0; i < 16; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+            tmem_st16(o_tmem + c * 16, o);
           }
         }
       };
-      // P = exp2(S*scale - m_ref) packed to 16 bit over the S columns; returns the row sum of this thread's half.
+      // 32 logits -> exp2(s*scale - m_ref) packed to 16 bit into 16 TMEM columns at `dst`; returns their sum.
       // Packed fp32 pairs: one FFMA2 scales and shifts two logits, one FADD2 adds two probabilities.
-      auto write_p = [&]() -> float {
+      auto exp_piece = [&](uint32_t (&a)[32], uint32_t dst) -> float {
         const float neg_m = (m_ref == -INFINITY) ? 0.f : -m_ref;
         const float2 sc2 = make_float2(p.scale_log2, p.scale_log2), nm2 = make_float2(neg_m, neg_m);
         float2 l2a = make_float2(0.f, 0.f), l2b = make_float2(0.f, 0.f);
+        uint32_t pk[16];
 #pragma unroll
-        for (int c = 0; c < kHalf / 32; ++c) {
-          uint32_t pk[16];
-#pragma unroll
-          for (int i = 0; i < 16; i += 2) {
-            const float2 t0 = __ffma2_rn(make_float2(s[c * 32 + 2 * i], s[c * 32 + 2 * i + 1]), sc2, nm2);
-            const float2 t1 = __ffma2_rn(make_float2(s[c * 32 + 2 * i + 2], s[c * 32 + 2 * i + 3]), sc2, nm2);
+        for (int i = 0; i < 16; i += 2) {
+          const float2 t0 = __ffma2_rn(make_float2(__uint_as_float(a[2 * i]), __uint_as_float(a[2 * i + 1])), sc2, nm2);
+          const float2 t1 =
+              __ffma2_rn(make_float2(__uint_as_float(a[2 * i + 2]), __uint_as_float(a[2 * i + 3])), sc2, nm2);
 #ifdef CVLLM_PROBE_NO_EXP  // timing probe only (wrong results): the loop without its MUFU work
-            const float2 e0 = t0, e1 = t1;
+          const float2 e0 = t0, e1 = t1;
 #else
-            // kPolyEvery: one exponential in every kPolyEvery is evaluated on the FMA pipe (ex2_poly) instead of the
-            // MUFU, whose 16 results / clk / SM make the 2 x 128 x 128 exponentials of a KV tile as long as its UMMAs
-            const bool py0 = kPolyEvery == 2, py1 = kPolyEvery == 2 || kPolyEvery == 4 || (kPolyEvery == 8 && (i & 2));
-            const float2 e0 = make_float2(ex2(t0.x), py0 ? ex2_poly(t0.y) : ex2(t0.y));
-            const float2 e1 = make_float2(ex2(t1.x), py1 ? ex2_poly(t1.y) : ex2(t1.y));
+          // kPolyEvery: one exponential in every kPolyEvery goes to the FMA pipe (ex2_poly).  A warp that issues a
+          // MUFU.EX2 is held for the 8 cycles its scheduler's 4-lane unit needs; with TWO softmax warps of a head on
+          // each scheduler the other warp's FMA-pipe work fills those cycles, which a lone warp could not (3.1).
+          const bool py0 = kPolyEvery == 2, py1 = kPolyEvery == 2 || kPolyEvery == 4 || (kPolyEvery == 8 && (i & 2));
+          const float2 e0 = make_float2(ex2(t0.x), py0 ? ex2_poly(t0.y) : ex2(t0.y));
+          const float2 e1 = make_float2(ex2(t1.x), py1 ? ex2_poly(t1.y) : ex2(t1.y));
 #endif
-            l2a = __fadd2_rn(l2a, e0);
-            l2b = __fadd2_rn(l2b, e1);
-            pk[i] = pack2<BF16>(e0.x, e0.y);
-            pk[i + 1] = pack2<BF16>(e1.x, e1.y);
-          }
-          tmem_st16(s_tmem + (c0 >> 1) + c * 16, pk);  // key k of the tile lives in 32-bit column k / 2
+          l2a = __fadd2_rn(l2a, e0);
+          l2b = __fadd2_rn(l2b, e1);
+          pk[i] = pack2<BF16>(e0.x, e0.y);
+          pk[i + 1] = pack2<BF16>(e1.x, e1.y);
         }
+        tmem_st16(dst, pk);
         return (l2a.x + l2b.x) + (l2a.y + l2b.y);
       };
 
@@ -413,7 +419,14 @@ prefill_attn2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
         // tile's maximum does (it never did after an earlier tile, or that tile would have rescaled).
         const bool need = (j == 0) || (m_run > m_ref + p.rescale_threshold);
         if (__any_sync(0xffffffffu, need)) rescale_to(fmaxf(m_ref, m_run));
-        l += write_p();
+        // P of my 64 keys goes over the X columns only (keys c0 + k -> 32-bit column c0 + k / 2): they are in
+        // registers by now, the Y columns stay intact for the second read, and neither thread of a row ever touches
+        // the other's columns.  The issuer reads P at columns [0, 32) and [64, 96) of the S buffer.
+        l += exp_piece(x, s_tmem + c0);
+        tmem_ld32(s_tmem + c0 + 32, x);  // Y again, into the same registers
+        tc_wait_ld();
+        mask(x, c0 + 32);
+        l += exp_piece(x, s_tmem + c0 + 16);
       }
       tc_wait_st();
       tc_fence_before();
