@@ -5,8 +5,8 @@
 //   spin      N warps polling mbarrier.try_wait on a barrier that completes only at the end
 //   ldtm      N warps reading 128 TMEM columns (tcgen05.ld x4 + wait) in a loop, as the softmax does with S
 //   sttm      ... and writing 64 columns back (tcgen05.st), as the softmax does with P
-// The operands are the constant 1.0 unless `random_data`: with random data the SAME instruction stream runs slower
-// (power management of the tensor pipe), which is what cuBLAS's measured 1658 TFLOP/s (74 % of nominal) also shows.
+// The operands are the constant 1.0 unless `random_data`; random operand data does NOT slow the stream (64.0 either way
+// over 20 M cycles), so the gap to cuBLAS's measured 1658 TFLOP/s is not a data-dependent throttle at this time scale.
 // build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -I compactor-vllm_b200/csrc -o tools/ubench/umma_mix tools/ubench/umma_mix.cu
 #include <cstdio>
 #include <cuda_runtime.h>
