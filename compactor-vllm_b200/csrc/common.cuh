@@ -86,6 +86,7 @@ struct TestOptions {
   std::atomic<int> eig_trace{0};
   std::atomic<int> snap_v1{0};                // 1: the mma.sync SnapKV kernels
   std::atomic<int> chunk_scores_v1{0};        // 1: the mma.sync chunk scorer (A/B against the tcgen05 one)
+  std::atomic<int> no_pdl{0};                 // 1: launch the short-kernel chains without programmatic dependent launch (A/B)
   std::atomic<int> grs_pairs{0};              // > 0: cap the CTA pairs of gemm_reduce (several virtual ranks on one GPU)
   std::atomic<int> grs_probe{0};              // gemm_reduce timing probes (bit mask; results are wrong)
   std::atomic<uint64_t> grs_debug_host_ptr{0};  // pinned host buffer for gemm_reduce's timeout records
@@ -102,6 +103,36 @@ int launch_decode_store(const void* key, const void* value, int64_t sk_b, int64_
                         int PS, int NLP, int elem_bytes, int reserved_batch, int lens_by_slot,
                         cvllm_stream_t stream);
 uint64_t launches();
+
+// ---------------------------------------------------------------------------
+// Programmatic dependent launch (a chain of short kernels on one stream): `launch_pdl` lets the NEXT kernel of the
+// stream be scheduled while this one is still running; a kernel launched that way calls `pdl_begin()` as its first
+// statement, which (a) allows ITS successor to be scheduled and (b) waits until every earlier kernel of the stream
+// has completed and its writes are visible.  Ordering and results are those of plain stream order; what disappears is
+// the scheduling gap between two kernels (3-5 us each, which is most of a 10 us selection pass).  Without the launch
+// attribute `pdl_begin()` is a no-op.  Captured launches become programmatic edges of the CUDA graph.
+// ---------------------------------------------------------------------------
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_begin() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                              Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = test_options().no_pdl.load() ? 0 : 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+#endif
 
 // ---------------------------------------------------------------------------
 // small device helpers

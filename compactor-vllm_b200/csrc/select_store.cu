@@ -54,6 +54,7 @@ __global__ void sel_init_kernel(const int32_t* __restrict__ cu, const int32_t* _
                                 const int32_t* __restrict__ batch_mapping,
                                 const int32_t* __restrict__ bh_lens, int B, int H, int reserved_batch,
                                 SelWs w) {
+  pdl_begin();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < B) {
     const int cnt = (cu[i + 1] - cu[i]) * H;
@@ -114,6 +115,7 @@ __global__ void __launch_bounds__(kPassThreads) sel_pass_kernel(const float* __r
                                                                 int64_t stride_n,
                                                                 const int32_t* __restrict__ cu, int H,
                                                                 int pass, SelWs w) {
+  pdl_begin();
   __shared__ uint32_t s_hist[PER_HEAD ? kMaxH * 256 : 256];
   __shared__ uint32_t s_prefix[kMaxH];
   __shared__ uint32_t s_active[kMaxH];
@@ -186,6 +188,7 @@ __global__ void __launch_bounds__(kPassThreads) sel_count_global_kernel(const fl
                                                                         int64_t stride_n,
                                                                         const int32_t* __restrict__ cu,
                                                                         int H, SelWs w) {
+  pdl_begin();
   __shared__ uint32_t s_gt[kMaxH], s_tie[kMaxH];
   const int b = blockIdx.y, tile = blockIdx.x;
   const int beg = cu[b], len = cu[b + 1] - beg;
@@ -221,6 +224,7 @@ __global__ void __launch_bounds__(kPassThreads) sel_resolve_kernel(const float* 
                                                                    const int32_t* __restrict__ batch_mapping,
                                                                    int H, int PS, int pad_to_page,
                                                                    int reserved_batch, SelWs w) {
+  pdl_begin();
   __shared__ uint32_t s_tiesel[kMaxH];
   __shared__ int s_warp[32];
   __shared__ int s_btile;
@@ -328,6 +332,7 @@ __global__ void __launch_bounds__(kPassThreads) sel_count_heads_kernel(const flo
                                                                        int64_t stride_n,
                                                                        const int32_t* __restrict__ cu,
                                                                        int H, SelWs w) {
+  pdl_begin();
   __shared__ uint32_t s_gt[kMaxH], s_tie[kMaxH], s_thr[kMaxH], s_act[kMaxH];
   const int b = blockIdx.y, tile = blockIdx.x;
   const int beg = cu[b], len = cu[b + 1] - beg;
@@ -363,6 +368,7 @@ __global__ void __launch_bounds__(kTileTok) sel_gather_kernel(
     const int32_t* __restrict__ cu, const int32_t* __restrict__ batch_mapping,
     const int32_t* __restrict__ page_table, int32_t* __restrict__ bh_lens, uint4* __restrict__ k_cache,
     uint4* __restrict__ v_cache, int H, int PS, int NLP, SelWs w) {
+  pdl_begin();
   __shared__ uint32_t s_gt_before[kMaxH], s_tie_before[kMaxH], s_gt_all[kMaxH], s_tie_all[kMaxH];
   __shared__ uint32_t s_thr[kMaxH], s_ties[kMaxH], s_act[kMaxH];
   __shared__ uint32_t s_wsel[kMaxH][kTileTok / 32], s_wtie[kMaxH][kTileTok / 32];
@@ -532,9 +538,8 @@ static void launch_sel_gather(dim3 grid, cudaStream_t st, const float* scores, i
                               int64_t sv_n, int64_t sv_h, const int32_t* cu, const int32_t* bm,
                               const int32_t* pt, int32_t* bh_lens, void* kc, void* vc, int H, int PS,
                               int NLP, const SelWs& w) {
-  sel_gather_kernel<V><<<grid, kTileTok, 0, st>>>(scores, s_stride_n, (const uint4*)keys,
-                                                  (const uint4*)vals, sk_n, sk_h, sv_n, sv_h, cu, bm, pt,
-                                                  bh_lens, (uint4*)kc, (uint4*)vc, H, PS, NLP, w);
+  launch_pdl(sel_gather_kernel<V>, grid, dim3(kTileTok), 0, st, scores, s_stride_n, (const uint4*)keys,
+             (const uint4*)vals, sk_n, sk_h, sv_n, sv_h, cu, bm, pt, bh_lens, (uint4*)kc, (uint4*)vc, H, PS, NLP, w);
 }
 
 extern "C" int cvllm_select_store_topk(const float* scores, int64_t s_stride_n, const void* keys,
@@ -576,14 +581,17 @@ extern "C" int cvllm_select_store_topk(const float* scores, int64_t s_stride_n, 
   const dim3 grid((N + kTileTok - 1) / kTileTok, B);
   sel_init_kernel<<<(B * HKV + 255) / 256, 256, 0, st>>>(cu_seqlens_k, num_retain, batch_mapping, bh_lens,
                                                          B, HKV, reserved_batch, w);
+  // eleven short kernels in a row, each dependent on the one before: programmatic dependent launch (common.cuh)
+  // removes the scheduling gap between them
+  const dim3 pb(kPassThreads);
   for (int pass = 0; pass < 4; ++pass)
-    sel_pass_kernel<false><<<grid, kPassThreads, 0, st>>>(scores, s_stride_n, cu_seqlens_k, HKV, pass, w);
-  sel_count_global_kernel<<<grid, kPassThreads, 0, st>>>(scores, s_stride_n, cu_seqlens_k, HKV, w);
-  sel_resolve_kernel<<<B, kPassThreads, 0, st>>>(scores, s_stride_n, cu_seqlens_k, batch_mapping, HKV, PS,
-                                                 pad_to_page, reserved_batch, w);
+    CVLLM_CHECK_CUDA(launch_pdl(sel_pass_kernel<false>, grid, pb, 0, st, scores, s_stride_n, cu_seqlens_k, HKV, pass, w));
+  CVLLM_CHECK_CUDA(launch_pdl(sel_count_global_kernel, grid, pb, 0, st, scores, s_stride_n, cu_seqlens_k, HKV, w));
+  CVLLM_CHECK_CUDA(launch_pdl(sel_resolve_kernel, dim3(B), pb, 0, st, scores, s_stride_n, cu_seqlens_k, batch_mapping,
+                              HKV, PS, pad_to_page, reserved_batch, w));
   for (int pass = 0; pass < 4; ++pass)
-    sel_pass_kernel<true><<<grid, kPassThreads, 0, st>>>(scores, s_stride_n, cu_seqlens_k, HKV, pass, w);
-  sel_count_heads_kernel<<<grid, kPassThreads, 0, st>>>(scores, s_stride_n, cu_seqlens_k, HKV, w);
+    CVLLM_CHECK_CUDA(launch_pdl(sel_pass_kernel<true>, grid, pb, 0, st, scores, s_stride_n, cu_seqlens_k, HKV, pass, w));
+  CVLLM_CHECK_CUDA(launch_pdl(sel_count_heads_kernel, grid, pb, 0, st, scores, s_stride_n, cu_seqlens_k, HKV, w));
   CVLLM_CHECK_LAUNCHES(12);
   // enough copy CTAs to fill the chip a few times over: 4 per tile at long prompts, 1 when the grid is already wide
   const int64_t gtiles = (int64_t)grid.x * grid.y;
