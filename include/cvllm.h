@@ -59,6 +59,13 @@ uint64_t cvllm_launch_count(void);
  *   "prefill_threshold" t    lazy-rescale threshold of the prefill softmax in log2 units (0 exercises the
  *                            O-correction path on every growing row max); negative = built-in default
  *   "decode_mode" m          decode_attn.cu profiling modes (0 = product), "decode_slots" n  TMA ring depth cap
+ *   "chunk_scores_v1" / "snap_v1" 1|0   the mma.sync scorers instead of the tcgen05 ones (A/B)
+ *   "no_pdl" 1|0             launch the selection chain without programmatic dependent launch (A/B)
+ *   "grs_pairs" n            cap the CTA pairs of cvllm_gemm_allreduce (several virtual ranks on one GPU: the tests)
+ *   "grs_rows_per_round" r   rows per reduce round of cvllm_gemm_allreduce (multiple of 256; 0 = default 256)
+ *   "grs_probe" mask         timing probes of cvllm_gemm_allreduce (results are wrong on purpose: 1 no TMA loads,
+ *                            2 no UMMA, 4 no stores, 8 no reduce, 16 no L2 hints)
+ *   "grs_debug_host_ptr" p   pinned host buffer (64 words per CTA) for cvllm_gemm_allreduce's timeout records
  * Returns CVLLM_E_ARG for an unknown name. */
 int cvllm_set_test_option(const char* name, double value);
 /* Profiling only: in a library built with -DCVLLM_DECODE_TRACE (tools/trace_decode.py) the next decode launches
