@@ -79,7 +79,7 @@ def test_world1_matches_fp32_gemm(options, dtype, m, n, k):
 @pytest.mark.parametrize("world,m,n,k", [(2, 1024, 512, 256), (2, 777, 512, 128), (4, 2048, 1024, 512),
                                          (4, 100, 256, 256), (8, 4096, 512, 512), (3, 1500, 768, 192)])
 def test_virtual_ranks_bit_exact_rank_order_sum(options, world, m, n, k):
-    dtype = torch.bfloat16
+    dtype = torch.float16 if (world, m) == (2, 777) else torch.bfloat16  # one case on the f16 instantiation
     x, w, shards = _shards(m, n, k, world, dtype, seed=world * 1000 + m)
     partial = [_run_world(1, m, n, [shards[r]])[0] for r in range(world)]  # each rank's own rounded GEMM
     acc = torch.zeros((m, n), dtype=torch.float32, device=x.device)
