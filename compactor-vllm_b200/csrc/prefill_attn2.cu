@@ -62,6 +62,32 @@ struct Prefill2Smem {
   uint32_t tmem_base;
 };
 
+// kPolyPairs = e: e of every 8 logit PAIRS take their exponentials on the FMA pipe (ex2_poly2) instead of the MUFU.
+// A warp that issues MUFU.EX2 is held for the 8 cycles its scheduler's 4-lane unit needs (59 % of a softmax warp's
+// active samples in the ncu source view); ten packed fp32x2 instructions do a PAIR.  Measured with the in-kernel trace
+// (cycles per KV tile, together with the converged-warp UMMA issue below): e = 0: 3161, 1: 3050, 2: 2881, 3: 2887,
+// 4: 3218 — beyond a third the FMA-pipe work outweighs the MUFU time it frees.
+#ifndef CVLLM_PREFILL_POLY_PAIRS
+#define CVLLM_PREFILL_POLY_PAIRS 2
+#endif
+constexpr int kPolyPairs = CVLLM_PREFILL_POLY_PAIRS;
+// 2^x for two values x <= ~8 with packed fp32x2 arithmetic: round-to-nearest split x = n + f (|f| <= 0.5), degree-3
+// polynomial in f (relative error ~1e-4, far below the 2^-9 rounding of P to 16 bits), exponent added as an integer.
+// Inputs below -125 (masked logits are -inf) flush to 2^-125, which the 16-bit P and the fp32 row sum take as 0.
+__device__ __forceinline__ float2 ex2_poly2(float2 x) {
+  x.x = fmaxf(x.x, -125.f);
+  x.y = fmaxf(x.y, -125.f);
+  const float2 magic = make_float2(12582912.f, 12582912.f);
+  const float2 t = __fadd2_rn(x, magic);
+  const float2 n = __fadd2_rn(t, make_float2(-12582912.f, -12582912.f));
+  const float2 f = __ffma2_rn(n, make_float2(-1.f, -1.f), x);
+  float2 p = __ffma2_rn(f, make_float2(0.05550357f, 0.05550357f), make_float2(0.24022652f, 0.24022652f));
+  p = __ffma2_rn(p, f, make_float2(0.69314575f, 0.69314575f));
+  p = __ffma2_rn(p, f, make_float2(1.f, 1.f));
+  return make_float2(__int_as_float(__float_as_int(p.x) + (__float_as_int(t.x) << 23)),
+                     __int_as_float(__float_as_int(p.y) + (__float_as_int(t.y) << 23)));
+}
+
 #ifdef CVLLM_PREFILL_TRACE  // profiling build only (tools/trace_prefill.py): clock64 stamps of CTA (0,0,0), first 256 KV tiles
 __device__ long long g_p2_trace[8][256];
 #define P2_TRACE(rowi, jj)                                                                              \
@@ -192,36 +218,29 @@ prefill_attn2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
 
     // S_t = Q_t . K_j^T  (K_j in ring entry 2j, already waited for)
     auto issue_qk = [&](int t, int j) {
-      if (lane == 0) {
-        const uint64_t k_desc = umma_smem_desc(smem_u32(sm.kv[slot_of(2 * j)]), 16, 1024);
-        const uint32_t s_tmem = tmem_u + t * kBN;
+      const uint64_t k_desc = umma_smem_desc(smem_u32(sm.kv[slot_of(2 * j)]), 16, 1024);
+      const uint32_t s_tmem = tmem_u + t * kBN;
 #pragma unroll
-        for (int kk = 0; kk < kHD / 16; ++kk) {
-          const uint32_t off = (kk >> 2) * kBoxBytes + (kk & 3) * 32;
-          umma_ss(s_tmem, desc_at(q_desc[t], off), desc_at(k_desc, off), idesc_qk, kk > 0 ? 1u : 0u);
-        }
-        umma_commit(&sm.s_full[t]);
-        if (t == 1) umma_commit(&sm.empty[slot_of(2 * j)]);  // K_j consumed by both heads
+      for (int kk = 0; kk < kHD / 16; ++kk) {
+        const uint32_t off = (kk >> 2) * kBoxBytes + (kk & 3) * 32;
+        umma_ss_warp(s_tmem, desc_at(q_desc[t], off), desc_at(k_desc, off), idesc_qk, kk > 0 ? 1u : 0u);
       }
-      __syncwarp();
+      umma_commit_warp(&sm.s_full[t]);
+      if (t == 1) umma_commit_warp(&sm.empty[slot_of(2 * j)]);
     };
-    // O_t += P_t . V_j  (V_j in ring entry 2j + 1, already waited for)
     auto issue_pv = [&](int t, int j) {
       mbar_wait(&sm.p_full[t], j & 1);
       P2_TRACE(2 * t, j);
       tc_fence_after();
-      if (lane == 0) {
-        const uint64_t v_desc = umma_smem_desc(smem_u32(sm.kv[slot_of(2 * j + 1)]), kBoxBytes, 1024);
-        const uint32_t p_tmem = tmem_u + t * kBN;
-        const uint32_t o_tmem = tmem_u + 256 + t * kHD;
+      const uint64_t v_desc = umma_smem_desc(smem_u32(sm.kv[slot_of(2 * j + 1)]), kBoxBytes, 1024);
+      const uint32_t p_tmem = tmem_u + t * kBN;
+      const uint32_t o_tmem = tmem_u + 256 + t * kHD;
 #pragma unroll
-        for (int kk = 0; kk < kBN / 16; ++kk)
-          umma_ts(o_tmem, p_tmem + kk * 8, desc_at(v_desc, kk * 2048), idesc_pv, (j > 0 || kk > 0) ? 1u : 0u);
-        if (t == 1) umma_commit(&sm.empty[slot_of(2 * j + 1)]);  // V_j consumed by both heads
-        umma_commit(&sm.o_done[t]);
-        if (j == n_tiles - 1) umma_commit(&sm.o_final[t]);
-      }
-      __syncwarp();
+      for (int kk = 0; kk < kBN / 16; ++kk)
+        umma_ts_warp(o_tmem, p_tmem + kk * 8, desc_at(v_desc, kk * 2048), idesc_pv, (j > 0 || kk > 0) ? 1u : 0u);
+      if (t == 1) umma_commit_warp(&sm.empty[slot_of(2 * j + 1)]);
+      umma_commit_warp(&sm.o_done[t]);
+      if (j == n_tiles - 1) umma_commit_warp(&sm.o_final[t]);
     };
     auto wait_v = [&](int j) {
       const int n = 2 * j + 1;
@@ -357,7 +376,14 @@ prefill_attn2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
 #ifdef CVLLM_PROBE_NO_EXP  // timing probe only (wrong results): the loop without its MUFU work — 7.6 ms, unchanged
             const float2 e0 = t0, e1 = t1;
 #else
-            const float2 e0 = make_float2(ex2(t0.x), ex2(t0.y)), e1 = make_float2(ex2(t1.x), ex2(t1.y));
+            // kPolyPairs = e: e of every 8 logit pairs (two loop trips, four pairs each... slots b0 b2 b1 b3 a1 a3 a0 a2)
+            const int slot = (i >> 1) & 3;
+            const bool p1 = (kPolyPairs >= 1 && slot == 0) || (kPolyPairs >= 2 && slot == 2) ||
+                            (kPolyPairs >= 3 && slot == 1) || (kPolyPairs >= 4 && slot == 3);
+            const bool p0 = (kPolyPairs >= 5 && slot == 1) || (kPolyPairs >= 6 && slot == 3) ||
+                            (kPolyPairs >= 7 && slot == 0) || (kPolyPairs >= 8 && slot == 2);
+            const float2 e0 = p0 ? ex2_poly2(t0) : make_float2(ex2(t0.x), ex2(t0.y));
+            const float2 e1 = p1 ? ex2_poly2(t1) : make_float2(ex2(t1.x), ex2(t1.y));
 #endif
             l2a = __fadd2_rn(l2a, e0);
             l2b = __fadd2_rn(l2b, e1);
