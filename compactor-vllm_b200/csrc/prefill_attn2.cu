@@ -57,6 +57,7 @@ struct Prefill2Smem {
   uint64_t q_full;
   uint64_t full[p2::kSlots], empty[p2::kSlots];
   uint64_t s_full[2], p_full[2];
+  uint64_t p_half[2];   // P of the tile's first 64 keys is in TMEM: the PV UMMAs of those keys may start
   uint64_t o_done[2];   // one phase per PV_t(i)
   uint64_t o_final[2];  // last PV_t complete
   uint32_t tmem_base;
@@ -65,11 +66,19 @@ struct Prefill2Smem {
 // kPolyPairs = e: e of every 8 logit PAIRS take their exponentials on the FMA pipe (ex2_poly2) instead of the MUFU.
 // A warp that issues MUFU.EX2 is held for the 8 cycles its scheduler's 4-lane unit needs (59 % of a softmax warp's
 // active samples in the ncu source view); ten packed fp32x2 instructions do a PAIR.  Measured with the in-kernel trace
-// (cycles per KV tile, together with the converged-warp UMMA issue below): e = 0: 3161, 1: 3050, 2: 2881, 3: 2887,
-// 4: 3218 — beyond a third the FMA-pipe work outweighs the MUFU time it frees.
+// (cycles per KV tile, together with the converged-warp UMMA issue below, P handed over at once): e = 0: 3161, 1: 3050,
+// 2: 2881, 3: 2887, 4: 3218 — beyond a third the FMA-pipe work outweighs the MUFU time it frees.
 #ifndef CVLLM_PREFILL_POLY_PAIRS
-#define CVLLM_PREFILL_POLY_PAIRS 2
+#define CVLLM_PREFILL_POLY_PAIRS 3
 #endif
+// P is handed to the issuer in two parts (the first kPSplit 32-key pieces, then the rest): the first PV UMMAs run while
+// the softmax group is still on the second part.  With the ELECT-loop issuer this LOST 3 % (the issuer stalled in the
+// middle of a group); with the converged-warp issue it takes another 230 cycles off the tile: trace, cycles per KV tile,
+// polynomial pairs 3 of 8: split 0: 2887, 1: 2678, 2: 2647, 3: 2668 (and 3021 with 4 of 8 pairs).
+#ifndef CVLLM_PREFILL_P_SPLIT
+#define CVLLM_PREFILL_P_SPLIT 2
+#endif
+constexpr int kPSplit = CVLLM_PREFILL_P_SPLIT;  // 32-key pieces of P handed to the issuer ahead of the rest (0: all at once)
 constexpr int kPolyPairs = CVLLM_PREFILL_POLY_PAIRS;
 // 2^x for two values x <= ~8 with packed fp32x2 arithmetic: round-to-nearest split x = n + f (|f| <= 0.5), degree-3
 // polynomial in f (relative error ~1e-4, far below the 2^-9 rounding of P to 16 bits), exponent added as an integer.
@@ -132,6 +141,7 @@ prefill_attn2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
     for (int t = 0; t < 2; ++t) {
       mbar_init(&sm.s_full[t], 1);
       mbar_init(&sm.p_full[t], 128);
+      mbar_init(&sm.p_half[t], 128);
       mbar_init(&sm.o_done[t], 1);
       mbar_init(&sm.o_final[t], 1);
     }
@@ -229,15 +239,29 @@ prefill_attn2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
       if (t == 1) umma_commit_warp(&sm.empty[slot_of(2 * j)]);
     };
     auto issue_pv = [&](int t, int j) {
-      mbar_wait(&sm.p_full[t], j & 1);
-      P2_TRACE(2 * t, j);
-      tc_fence_after();
       const uint64_t v_desc = umma_smem_desc(smem_u32(sm.kv[slot_of(2 * j + 1)]), kBoxBytes, 1024);
       const uint32_t p_tmem = tmem_u + t * kBN;
       const uint32_t o_tmem = tmem_u + 256 + t * kHD;
+#if CVLLM_PREFILL_P_SPLIT > 0
+      mbar_wait(&sm.p_half[t], j & 1);
+      P2_TRACE(2 * t, j);
+      tc_fence_after();
+#pragma unroll
+      for (int kk = 0; kk < 2 * kPSplit; ++kk)
+        umma_ts_warp(o_tmem, p_tmem + kk * 8, desc_at(v_desc, kk * 2048), idesc_pv, (j > 0 || kk > 0) ? 1u : 0u);
+      mbar_wait(&sm.p_full[t], j & 1);
+      tc_fence_after();
+#pragma unroll
+      for (int kk = 2 * kPSplit; kk < kBN / 16; ++kk)
+        umma_ts_warp(o_tmem, p_tmem + kk * 8, desc_at(v_desc, kk * 2048), idesc_pv, 1u);
+#else
+      mbar_wait(&sm.p_full[t], j & 1);
+      P2_TRACE(2 * t, j);
+      tc_fence_after();
 #pragma unroll
       for (int kk = 0; kk < kBN / 16; ++kk)
         umma_ts_warp(o_tmem, p_tmem + kk * 8, desc_at(v_desc, kk * 2048), idesc_pv, (j > 0 || kk > 0) ? 1u : 0u);
+#endif
       if (t == 1) umma_commit_warp(&sm.empty[slot_of(2 * j + 1)]);
       umma_commit_warp(&sm.o_done[t]);
       if (j == n_tiles - 1) umma_commit_warp(&sm.o_final[t]);
@@ -301,6 +325,7 @@ prefill_attn2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
       tc_fence_after();
 #ifdef CVLLM_PROBE_NO_SOFTMAX  // timing probe only (wrong results): the issuer / TMA side alone — 6.4 ms at 32K
       tc_fence_before();
+      mbar_arrive(&sm.p_half[t]);
       mbar_arrive(&sm.p_full[t]);
       if (quad == 0) P2_TRACE(5 + 2 * t, j);
       continue;
@@ -391,6 +416,13 @@ prefill_attn2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
             pk[i + 1] = pack2<BF16>(e1.x, e1.y);
           }
           tmem_st16(s_tmem + c * 16, pk);
+#if CVLLM_PREFILL_P_SPLIT > 0
+          if (c == kPSplit - 1) {  // the first part of P (and any O rescale before it) is in TMEM
+            tc_wait_st();
+            tc_fence_before();
+            mbar_arrive(&sm.p_half[t]);
+          }
+#endif
         }
         return (l2a.x + l2b.x) + (l2a.y + l2b.y);
       };
