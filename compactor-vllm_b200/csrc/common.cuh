@@ -86,7 +86,7 @@ struct TestOptions {
   std::atomic<int> eig_trace{0};
   std::atomic<int> snap_v1{0};                // 1: the mma.sync SnapKV kernels
   std::atomic<int> chunk_scores_v1{0};        // 1: the mma.sync chunk scorer (A/B against the tcgen05 one)
-  std::atomic<int> no_pdl{0};                 // 1: launch the short-kernel chains without programmatic dependent launch (A/B)
+  std::atomic<int> pdl{0};                    // 1: launch the selection chain with programmatic dependent launch (A/B; off in the product)
   std::atomic<int> grs_pairs{0};              // > 0: cap the CTA pairs of gemm_reduce (several virtual ranks on one GPU)
   std::atomic<int> grs_probe{0};              // gemm_reduce timing probes (bit mask; results are wrong)
   std::atomic<uint64_t> grs_debug_host_ptr{0};  // pinned host buffer for gemm_reduce's timeout records
@@ -108,9 +108,11 @@ uint64_t launches();
 // Programmatic dependent launch (a chain of short kernels on one stream): `launch_pdl` lets the NEXT kernel of the
 // stream be scheduled while this one is still running; a kernel launched that way calls `pdl_begin()` as its first
 // statement, which (a) allows ITS successor to be scheduled and (b) waits until every earlier kernel of the stream
-// has completed and its writes are visible.  Ordering and results are those of plain stream order; what disappears is
-// the scheduling gap between two kernels (3-5 us each, which is most of a 10 us selection pass).  Without the launch
-// attribute `pdl_begin()` is a no-op.  Captured launches become programmatic edges of the CUDA graph.
+// has completed and its writes are visible.  Ordering and results are those of plain stream order.
+// OFF by default (test option "pdl" = 1 turns it on): measured on the selection chain it takes 15-19 us off the eager
+// chain run alone and nothing off its CUDA-graph replay, but INSIDE the prefill step — where every SM is held by an
+// attention CTA that uses all its shared memory and registers — the early-scheduled CTAs sit on SMs while they wait,
+// and the step gets 1-2 % slower (tools/ab_pdl.py, tools/ab_overlap.py).  Without the attribute `pdl_begin()` is a no-op.
 // ---------------------------------------------------------------------------
 #ifdef __CUDACC__
 __device__ __forceinline__ void pdl_begin() {
@@ -127,7 +129,7 @@ inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr[0].val.programmaticStreamSerializationAllowed = test_options().no_pdl.load() ? 0 : 1;
+  attr[0].val.programmaticStreamSerializationAllowed = test_options().pdl.load() ? 1 : 0;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);

@@ -103,7 +103,7 @@ extern "C" int cvllm_set_test_option(const char* name, double value) {
   else if (!strcmp(name, "decode_slots")) o.decode_slots = (int)value;
   else if (!strcmp(name, "chunk_scores_v1")) o.chunk_scores_v1 = (int)value;
   else if (!strcmp(name, "snap_v1")) o.snap_v1 = (int)value;
-  else if (!strcmp(name, "no_pdl")) o.no_pdl = (int)value;
+  else if (!strcmp(name, "pdl")) o.pdl = (int)value;
   else if (!strcmp(name, "grs_pairs")) o.grs_pairs = (int)value;
   else if (!strcmp(name, "grs_probe")) o.grs_probe = (int)value;
   else if (!strcmp(name, "grs_debug_host_ptr")) o.grs_debug_host_ptr = (uint64_t)value;

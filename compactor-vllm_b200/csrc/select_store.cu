@@ -581,8 +581,8 @@ extern "C" int cvllm_select_store_topk(const float* scores, int64_t s_stride_n, 
   const dim3 grid((N + kTileTok - 1) / kTileTok, B);
   sel_init_kernel<<<(B * HKV + 255) / 256, 256, 0, st>>>(cu_seqlens_k, num_retain, batch_mapping, bh_lens,
                                                          B, HKV, reserved_batch, w);
-  // eleven short kernels in a row, each dependent on the one before: programmatic dependent launch (common.cuh)
-  // removes the scheduling gap between them
+  // eleven short kernels in a row, each dependent on the one before; launch_pdl is a plain launch unless the test
+  // option "pdl" is set (common.cuh has the measurements)
   const dim3 pb(kPassThreads);
   for (int pass = 0; pass < 4; ++pass)
     CVLLM_CHECK_CUDA(launch_pdl(sel_pass_kernel<false>, grid, pb, 0, st, scores, s_stride_n, cu_seqlens_k, HKV, pass, w));

@@ -60,7 +60,7 @@ uint64_t cvllm_launch_count(void);
  *                            O-correction path on every growing row max); negative = built-in default
  *   "decode_mode" m          decode_attn.cu profiling modes (0 = product), "decode_slots" n  TMA ring depth cap
  *   "chunk_scores_v1" / "snap_v1" 1|0   the mma.sync scorers instead of the tcgen05 ones (A/B)
- *   "no_pdl" 1|0             launch the selection chain without programmatic dependent launch (A/B)
+ *   "pdl" 1|0                launch the selection chain with programmatic dependent launch (A/B; off by default)
  *   "grs_pairs" n            cap the CTA pairs of cvllm_gemm_allreduce (several virtual ranks on one GPU: the tests)
  *   "grs_rows_per_round" r   rows per reduce round of cvllm_gemm_allreduce (multiple of 256; 0 = default 256)
  *   "grs_probe" mask         timing probes of cvllm_gemm_allreduce (results are wrong on purpose: 1 no TMA loads,

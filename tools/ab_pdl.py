@@ -1,5 +1,5 @@
 """COMPACTOR compression chain (32K and 4K tokens) with and without programmatic dependent launch, eager and as a CUDA
-graph, alternating.  `no_pdl` is the library's test option (launch_pdl then passes attribute value 0)."""
+graph, alternating.  `pdl` is the library's test option (off by default: launch_pdl then passes attribute value 0)."""
 import sys
 from pathlib import Path
 
@@ -12,7 +12,7 @@ from compactor_vllm import _native as N  # noqa: E402
 
 
 def opt(v):
-    N.check(N.lib().cvllm_set_test_option(b"no_pdl", float(v)), "no_pdl")
+    N.check(N.lib().cvllm_set_test_option(b"pdl", float(1 - v)), "pdl")
 
 
 def timed(fn, reps):
